@@ -1,0 +1,182 @@
+/*
+ * yolohot.h — C ABI of the B200-native (sm_100a) detection hot path for yolo-dl.
+ *
+ * This is the drop-in boundary: every entry point below replaces the body of one
+ * Rust method of the reference (jerry73204/yolo-dl).  The Rust side keeps its
+ * signatures and only marshals `Tensor::data_ptr()`s and shapes; see
+ * INTEGRATION.md for the `extern "C"` block a maintainer would add.
+ *
+ * Conventions:
+ *   - every `*_dev` / head / output pointer is caller-owned DEVICE memory on the
+ *     device the workspace was created for; the library never frees caller memory;
+ *   - `stream` is a `cudaStream_t` passed as `void*` (NULL = legacy default stream,
+ *     which is what tch 0.7 runs on);
+ *   - no entry point synchronises the device unless its comment says so; counts
+ *     (`M`, `K`) are produced in device memory, `yh_read_counts` is the one
+ *     synchronising read (the reference already syncs there: `nonzero`, host matcher);
+ *   - return value: 0 (YH_OK) or a YhStatus; `yh_last_error()` gives the text
+ *     (thread-local), the Rust wrapper maps it to `anyhow::Error` / panic as today;
+ *   - there is NO CPU fallback: without a CUDA device every compute call fails.
+ *
+ * Layout of one head tensor (input of Detect2D, `tch-modules/src/detect_2d.rs:66`):
+ *   contiguous f32 `[B, A*(5+C), H, W]` VIEWED as `[B, 5+C, A, H, W]`, i.e.
+ *   channel = entry*A + anchor, entries 0=cy 1=cx 2=h 3=w 4=obj 5..=class.
+ * Flat instance index inside an image (`merged_dense_detection.rs:374-376`):
+ *   flat = layer.flat_start + col + W*(row + H*anchor).
+ */
+#ifndef YOLOHOT_H
+#define YOLOHOT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define YH_MAX_LAYERS 8
+#define YH_MAX_ANCHORS 8
+
+typedef enum YhStatus {
+  YH_OK = 0,
+  YH_ERR_INVALID = 1,     /* bad argument (shape, null pointer, unsupported option) */
+  YH_ERR_CUDA = 2,        /* a CUDA runtime call failed (text in yh_last_error) */
+  YH_ERR_CAPACITY = 3,    /* an output or workspace buffer was too small */
+  YH_ERR_UNSUPPORTED = 4  /* valid in the reference but outside this path */
+} YhStatus;
+
+/* `yolo-dl/src/loss/misc.rs:14-21` BoxMetric */
+typedef enum YhBoxMetric {
+  YH_METRIC_IOU = 0,
+  YH_METRIC_GIOU = 1,
+  YH_METRIC_DIOU = 2,
+  YH_METRIC_CIOU = 3,
+  YH_METRIC_HAUSDORFF = 4
+} YhBoxMetric;
+
+/* tch `Reduction` as used by `loss_.rs:301-319` (None returns per-row tensors and is
+ * not part of the scalar-loss ABI). */
+typedef enum YhReduction { YH_REDUCTION_MEAN = 0, YH_REDUCTION_SUM = 1 } YhReduction;
+
+/* One detection layer = one `DetectionInfo` (`merged_dense_detection.rs:497-507`)
+ * plus what `Detect2D` holds (`detect_2d.rs:33-39`). Anchors are RATIO units (h, w)
+ * in f64 exactly as the reference stores them (`Ratio<HW<R64>>`); the decode casts
+ * them to f32 (`detect_2d.rs:203-209`), the matcher uses them as f64
+ * (`pred_target_matching.rs:141`). */
+typedef struct YhLayer {
+  int32_t H, W, A, _pad;
+  int64_t flat_start; /* DetectionInfo.flat_index_range.start */
+  double anchor_h[YH_MAX_ANCHORS];
+  double anchor_w[YH_MAX_ANCHORS];
+} YhLayer;
+
+/* `YoloLossInit` (`yolo-dl/src/loss/loss_.rs:21-36`, defaults `:169-189`), BCE kinds only. */
+typedef struct YhLossCfg {
+  int32_t box_metric;   /* YhBoxMetric; default DIoU */
+  int32_t reduction;    /* YhReduction; default Mean */
+  double iou_loss_weight;            /* 0.05 */
+  double classification_loss_weight; /* 0.58 */
+  double objectness_loss_weight;     /* 1.0 */
+  double smooth_classification_coef; /* 0.01 */
+  double smooth_objectness_coef;     /* 0.0 */
+  int32_t has_objectness_pos_weight; /* 0 */
+  int32_t _pad;
+  double objectness_pos_weight;
+} YhLossCfg;
+
+typedef struct YhWorkspace YhWorkspace;
+
+/* Sizes the per-module scratch (slot tables, candidate lists, partial sums).
+ * Replaces nothing in the reference; created by the module constructors
+ * (`Detect2DInit::build` detect_2d.rs:12, `YoloLossInit::build` loss_.rs:39,
+ * `NonMaxSuppressionInit::build` nms.rs:28).
+ *   max_batch        largest B of any call
+ *   max_instances    largest N = sum_l A*H*W
+ *   cand_per_image   capacity of the per-image NMS candidate list */
+int yh_workspace_create(int device, int max_batch, int64_t max_instances,
+                        int cand_per_image, YhWorkspace** out);
+int yh_workspace_destroy(YhWorkspace* ws);
+const char* yh_last_error(void);
+const char* yh_version(void);
+
+/* ---- a1: Detect2D::forward (`tch-modules/src/detect_2d.rs:42-152`) -------------------
+ * cy = (2*sigmoid(x0) - 0.5)/H + row/H ; cx likewise with W ;
+ * h  = (2*sigmoid(x2))^2 * anchor_h   ; w likewise.  obj/class logits stay views of `head`.
+ * Output element (b, a, row, col) is written at out[b*out_batch_stride + (a*H+row)*W + col]:
+ * pass stride A*H*W for the four `[B,1,A,H,W]` tensors of DenseDetectionTensor, or the
+ * merged stride N with pointers pre-offset by flat_start to write straight into
+ * MergedDenseDetection's `[B,1,N]` planes (`merged_dense_detection.rs:60-91`). */
+int yh_decode(const float* head, int B, int C, const YhLayer* layer,
+              float* cy, float* cx, float* h, float* w, int64_t out_batch_stride,
+              void* stream);
+
+/* a1+a3 fused: all layers in ONE launch, straight into the merged
+ * `[B,1,N]` planes (batch stride = out_batch_stride >= N). */
+int yh_decode_merged(const float* const* heads, const YhLayer* layers, int L, int B, int C,
+                     float* cy, float* cx, float* h, float* w, int64_t out_batch_stride,
+                     void* stream);
+
+/* ---- a4: CyCxHWMatcher::match_bboxes (`yolo-dl/src/loss/pred_target_matching.rs:51-276`)
+ * gt_dev: [G,5] f64 rows (cy, cx, h, w, class) in ratio units, images concatenated;
+ * gt_offsets_dev: [B+1] int32 prefix offsets into gt_dev.
+ * Outputs (capacity rows each), sorted by (batch, flat):
+ *   out_batch/out_flat  FlatIndexTensor {batches, flats}       (:238-241)
+ *   out_gt              row of gt_dev that won the slot
+ *   out_target          [cap,4] f32 cy,cx,h,w of that GT        (:247)
+ *   out_class           i64 class                               (:248)
+ *   out_M_dev           int32 count M (device); M > capacity sets YH_ERR_CAPACITY at
+ *                       the next yh_read_counts.
+ * Decisions are taken in f64 with the reference's operation order (no FMA). */
+int yh_assign(YhWorkspace* ws, const double* gt_dev, const int32_t* gt_offsets_dev, int B,
+              const YhLayer* layers, int L, int rect4, double anchor_scale_thresh,
+              int64_t* out_batch, int64_t* out_flat, int32_t* out_gt, float* out_target,
+              int64_t* out_class, int32_t* out_M_dev, int capacity, void* stream);
+
+/* ---- a5..a11: YoloLoss::forward + autograd backward (`yolo-dl/src/loss/loss_.rs:227-277`)
+ * Reads the L head tensors and the matches of yh_assign; writes
+ *   losses4_dev   [total, iou, classification, objectness]            (:258-273)
+ *   iou_score_dev [cap] box metric per matched row (nullable)          (:296-299)
+ *   pred_rows_dev [cap, 5+C] gathered cy,cx,h,w,obj_logit,class_logit — the
+ *                 `MatchingOutput.pred` rows (`merged_dense_detection.rs:280-307`), nullable
+ *   grad_heads    L device pointers, each `[B, A*(5+C), H, W]`: d total_loss / d head,
+ *                 i.e. what `total_loss.backward()` delivers to the backbone
+ *                 (`train/src/train/single_gpu.rs:161-168`). NULL = forward only. */
+int yh_loss_fwd_bwd(YhWorkspace* ws, const float* const* heads, const YhLayer* layers, int L,
+                    int B, int C, const int64_t* m_batch, const int64_t* m_flat,
+                    const float* m_target, const int64_t* m_class, const int32_t* M_dev,
+                    int capacity, const YhLossCfg* cfg, float* losses4_dev,
+                    float* iou_score_dev, float* pred_rows_dev, float* const* grad_heads,
+                    void* stream);
+
+/* ---- a12+a13: NonMaxSuppression::forward (`yolo-dl/src/loss/nms.rs:72-170`) incl. the
+ * grouped greedy NMS of tch_nms::nms_by_scores (call site nms.rs:142-148).
+ * conf = sigmoid(obj)*sigmoid(cls); candidates: sigmoid(obj) >= thr && conf >= thr (f32
+ * compare, nms.rs:97-99); group = batch (by_class=0) or batch*C+class (nms.rs:129-133).
+ * Kept rows are emitted ordered by (batch, score desc, class*N+instance asc):
+ *   kb/kc/ki  i64 batches/classes/instances ; tlbr [cap,4] f32 (t,l,b,r) ; conf [cap]
+ *   out_K_dev int32 count (device).
+ * SYNCHRONISES the stream once (candidate counts, as `nonzero` does at nms.rs:100). */
+int yh_nms(YhWorkspace* ws, const float* const* heads, const YhLayer* layers, int L, int B,
+           int C, double confidence_threshold, double iou_threshold, int suppress_by_class,
+           int64_t* kb, int64_t* kc, int64_t* ki, float* tlbr, float* conf,
+           int32_t* out_K_dev, int capacity, void* stream);
+
+/* ---- a14: YoloInference::forward post-pass (`yolo-dl/src/loss/inference.rs:50-77`):
+ * among kept rows of the same (batch, instance) keep the one with max confidence.
+ * In-place compaction of the yh_nms outputs; *io_K_dev updated. */
+int yh_inference_pick(YhWorkspace* ws, int64_t* kb, int64_t* kc, int64_t* ki, float* tlbr,
+                      float* conf, int32_t* io_K_dev, int capacity, void* stream);
+
+/* Synchronising read of device-side counters; returns YH_ERR_CAPACITY if any call since
+ * the last read overflowed a buffer. Any pointer may be NULL. */
+int yh_read_counts(YhWorkspace* ws, const int32_t* M_dev, int32_t* M_host,
+                   const int32_t* K_dev, int32_t* K_host, void* stream);
+
+/* Number of kernels this library has launched on the calling thread since the last
+ * reset (bench.py's `gpu_launches`). */
+int64_t yh_launch_count(int reset);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* YOLOHOT_H */

@@ -1,0 +1,255 @@
+// assign.cu — K2: training target assignment on the device
+// (CyCxHWMatcher::match_bboxes, yolo-dl/src/loss/pred_target_matching.rs:51-276).
+//
+// The reference folds (GT x layer x anchor x neighbour-cell) entries into a HashMap keyed by
+// (batch, layer, anchor, row, col); on a key collision the GT whose centre is closer to the
+// cell centre wins, strict '<', so the earlier GT keeps ties (:180-217).  Collisions only
+// happen between GTs of the SAME image, so one CTA owns one image: its GT boxes are staged in
+// shared memory, its N slots live in an L2-resident slice of the workspace and the fold
+// becomes two order-independent atomicMin passes:
+//   pass A: slot_dist[flat] = min over entries of bits(dist^2)        (f64, >= 0 => monotone)
+//   pass B: slot_gt[flat]   = min GT index among entries with dist^2 == slot_dist[flat]
+// = "smallest distance, then earliest GT", exactly the fold's result for any entry order.
+// All decisions use f64 and the reference's operation order; products and sums are written
+// with __dmul_rn/__dadd_rn so no FMA can change a floor(), a '< 0.5' or a distance tie.
+// A second kernel turns the slot table into the (batch, flat)-sorted match list.
+#include <math.h>
+
+#include "common.cuh"
+
+namespace yh {
+
+constexpr int kAssignThreads = 512;
+constexpr int kMaxGtSmem = 1024;  // GT rows staged per pass
+
+struct AssignTab {
+  int L, N, rect4;
+  double thresh;
+  int H[YH_MAX_LAYERS], W[YH_MAX_LAYERS], A[YH_MAX_LAYERS], start[YH_MAX_LAYERS];
+  double ah[YH_MAX_LAYERS][YH_MAX_ANCHORS], aw[YH_MAX_LAYERS][YH_MAX_ANCHORS];
+};
+
+// One (GT, layer, anchor) entry -> up to 5 cells (pred_target_matching.rs:87-150).
+// f(flat, dist_bits) is called for every in-range neighbour cell.
+template <typename F>
+__device__ __forceinline__ void for_each_cell(const AssignTab& t, int l, int a, double gcy,
+                                              double gcx, double gh, double gw, F f) {
+  // anchor-ratio filter (:139-150)
+  const double ah = t.ah[l][a], aw = t.aw[l][a];
+  const bool bounded = (gh / ah <= t.thresh) && (ah / gh <= t.thresh) && (gw / aw <= t.thresh) &&
+                       (aw / gw <= t.thresh);
+  if (!bounded) return;
+  // Transform::from_sizes_exact(unit, feature): sy = H/1, ty = 0 - 0*sy; cy*sy + ty (:88-94,
+  // bbox/src/transform.rs:16-37, bbox/src/cycxhw.rs:40-47)
+  const double Hd = (double)t.H[l], Wd = (double)t.W[l];
+  const double sy = Hd / 1.0, sx = Wd / 1.0;
+  const double ty = __dsub_rn(0.0, __dmul_rn(0.0, sy)), tx = __dsub_rn(0.0, __dmul_rn(0.0, sx));
+  const double cy = __dadd_rn(__dmul_rn(gcy, sy), ty);
+  const double cx = __dadd_rn(__dmul_rn(gcx, sx), tx);
+  const double fy = floor(cy), fx = floor(cx);
+  const long long row = (long long)fy, col = (long long)fx;
+  const double cy_fract = cy - trunc(cy), cx_fract = cx - trunc(cx);  // f64::fract
+  long long rr[5], cc[5];
+  int n = 0;
+  rr[n] = row; cc[n] = col; ++n;                                         // centre
+  if (cy_fract < 0.5) { rr[n] = row - 1; cc[n] = col; ++n; }             // top
+  if (cx_fract < 0.5) { rr[n] = row; cc[n] = col - 1; ++n; }             // left
+  if (t.rect4 && cy_fract > 0.5) { rr[n] = row + 1; cc[n] = col; ++n; }  // bottom (Rect4)
+  if (t.rect4 && cx_fract > 0.5) { rr[n] = row; cc[n] = col + 1; ++n; }  // right  (Rect4)
+  for (int i = 0; i < n; ++i) {
+    if (rr[i] < 0 || rr[i] >= t.H[l] || cc[i] < 0 || cc[i] >= t.W[l]) continue;  // (:112-116)
+    // distance of the GT centre to the cell centre, ratio units (:193-204)
+    const double pcy = __dadd_rn((double)rr[i], 0.5) / Hd;
+    const double pcx = __dadd_rn((double)cc[i], 0.5) / Wd;
+    const double dy = __dsub_rn(gcy, pcy), dx = __dsub_rn(gcx, pcx);
+    const double d2 = __dadd_rn(__dmul_rn(dy, dy), __dmul_rn(dx, dx));
+    const int flat = t.start[l] + (int)cc[i] + t.W[l] * ((int)rr[i] + t.H[l] * a);
+    f(flat, (unsigned long long)__double_as_longlong(d2));
+  }
+}
+
+__global__ void __launch_bounds__(kAssignThreads)
+assign_slots_kernel(const AssignTab t, const double* __restrict__ gt,
+                    const int* __restrict__ gt_off, unsigned long long* __restrict__ slot_dist,
+                    int* __restrict__ slot_gt, int* __restrict__ img_count) {
+  __shared__ double s_gt[kMaxGtSmem][4];
+  __shared__ int s_cnt[kAssignThreads / 32];
+  const int b = blockIdx.x;
+  const int g0 = gt_off[b], g1 = gt_off[b + 1];
+  const int ng = g1 - g0;
+  unsigned long long* sd = slot_dist + (size_t)b * (size_t)t.N;
+  int* sg = slot_gt + (size_t)b * (size_t)t.N;
+
+  for (int i = threadIdx.x; i < t.N; i += kAssignThreads) {
+    sd[i] = ~0ull;
+    sg[i] = 0x7fffffff;
+  }
+  __syncthreads();
+
+  // total anchors over layers, and prefix for (layer, anchor) enumeration
+  int la_total = 0;
+  for (int l = 0; l < t.L; ++l) la_total += t.A[l];
+
+  for (int pass = 0; pass < 2; ++pass) {
+    for (int base = 0; base < ng; base += kMaxGtSmem) {
+      const int chunk = min(kMaxGtSmem, ng - base);
+      __syncthreads();
+      for (int i = threadIdx.x; i < chunk * 4; i += kAssignThreads) {
+        const int g = i >> 2, k = i & 3;
+        s_gt[g][k] = gt[(size_t)(g0 + base + g) * 5 + k];
+      }
+      __syncthreads();
+      const int work = chunk * la_total;
+      for (int wi = threadIdx.x; wi < work; wi += kAssignThreads) {
+        const int g = wi / la_total;
+        int r = wi - g * la_total;
+        int l = 0;
+        while (r >= t.A[l]) { r -= t.A[l]; ++l; }
+        const double gh = s_gt[g][2], gw = s_gt[g][3];
+        // abs_diff_eq!(h, 0.0) with the default f64 epsilon (:65-68)
+        if (fabs(gh) <= 2.220446049250313e-16 || fabs(gw) <= 2.220446049250313e-16) continue;
+        const int gidx = base + g;
+        if (pass == 0) {
+          for_each_cell(t, l, r, s_gt[g][0], s_gt[g][1], gh, gw,
+                        [&](int flat, unsigned long long d) { atomicMin(&sd[flat], d); });
+        } else {
+          for_each_cell(t, l, r, s_gt[g][0], s_gt[g][1], gh, gw,
+                        [&](int flat, unsigned long long d) {
+                          if (__ldcg(&sd[flat]) == d) atomicMin(&sg[flat], gidx);
+                        });
+        }
+      }
+    }
+    __syncthreads();
+  }
+
+  // matches of this image
+  int local = 0;
+  for (int i = threadIdx.x; i < t.N; i += kAssignThreads)
+    local += (__ldcg(&sg[i]) != 0x7fffffff) ? 1 : 0;
+  for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
+  if ((threadIdx.x & 31) == 0) s_cnt[threadIdx.x >> 5] = local;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int tot = 0;
+    for (int i = 0; i < kAssignThreads / 32; ++i) tot += s_cnt[i];
+    img_count[b] = tot;
+  }
+}
+
+// Ordered compaction of the slot table into the match list, sorted by (batch, flat).
+__global__ void __launch_bounds__(kAssignThreads)
+assign_emit_kernel(int N, int B, const double* __restrict__ gt, const int* __restrict__ gt_off,
+                   const int* __restrict__ slot_gt, const int* __restrict__ img_count,
+                   long long* __restrict__ out_batch, long long* __restrict__ out_flat,
+                   int* __restrict__ out_gt, float* __restrict__ out_target,
+                   long long* __restrict__ out_class, int* __restrict__ out_M, int capacity,
+                   int* __restrict__ err_flag) {
+  __shared__ int s_warp[kAssignThreads / 32];
+  __shared__ int s_base;
+  const int b = blockIdx.x;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+
+  // offset of this image = sum of counts of earlier images
+  int part = 0;
+  for (int i = threadIdx.x; i < b; i += kAssignThreads) part += img_count[i];
+  for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+  if (lane == 0) s_warp[wid] = part;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int tot = 0;
+    for (int i = 0; i < kAssignThreads / 32; ++i) tot += s_warp[i];
+    s_base = tot;
+    if (b == B - 1) {
+      const int M = tot + img_count[b];
+      *out_M = M;
+      if (M > capacity) atomicOr(err_flag, 1);
+    }
+  }
+  __syncthreads();
+  int base = s_base;
+  const int g0 = gt_off[b];
+  const int* sg = slot_gt + (size_t)b * (size_t)N;
+
+  for (int tile = 0; tile < N; tile += kAssignThreads) {
+    const int i = tile + threadIdx.x;
+    const int g = (i < N) ? sg[i] : 0x7fffffff;
+    const bool hit = g != 0x7fffffff;
+    const unsigned m = __ballot_sync(0xffffffffu, hit);
+    __syncthreads();  // s_warp reuse
+    if (lane == 0) s_warp[wid] = __popc(m);
+    __syncthreads();
+    int before = 0, total = 0;
+#pragma unroll
+    for (int k = 0; k < kAssignThreads / 32; ++k) {
+      const int c = s_warp[k];
+      if (k < wid) before += c;
+      total += c;
+    }
+    if (hit) {
+      const int pos = base + before + __popc(m & ((1u << lane) - 1u));
+      if (pos < capacity) {
+        const int grow = g0 + g;
+        out_batch[pos] = b;
+        out_flat[pos] = i;
+        out_gt[pos] = grow;
+        const double* r = gt + (size_t)grow * 5;
+        out_target[(size_t)pos * 4 + 0] = (float)r[0];  // rect.cast::<f32>() (:247)
+        out_target[(size_t)pos * 4 + 1] = (float)r[1];
+        out_target[(size_t)pos * 4 + 2] = (float)r[2];
+        out_target[(size_t)pos * 4 + 3] = (float)r[3];
+        out_class[pos] = (long long)r[4];
+      }
+    }
+    base += total;
+  }
+}
+
+}  // namespace yh
+
+extern "C" int yh_assign(YhWorkspace* ws, const double* gt_dev, const int32_t* gt_offsets_dev,
+                         int B, const YhLayer* layers, int L, int rect4,
+                         double anchor_scale_thresh, int64_t* out_batch, int64_t* out_flat,
+                         int32_t* out_gt, float* out_target, int64_t* out_class,
+                         int32_t* out_M_dev, int capacity, void* stream) {
+  using namespace yh;
+  YH_REQUIRE(ws != nullptr, "workspace is NULL");
+  YH_REQUIRE(gt_offsets_dev != nullptr, "gt_offsets is NULL");
+  YH_REQUIRE(out_batch && out_flat && out_gt && out_target && out_class && out_M_dev,
+             "output pointer is NULL");
+  YH_REQUIRE(B >= 1 && B <= ws->max_batch, "B=%d outside 1..max_batch=%d", B, ws->max_batch);
+  // CyCxHWMatcherInit::build (:32-35)
+  YH_REQUIRE(anchor_scale_thresh >= 1.0, "anchor_scale_thresh must be greater than or equal to 1");
+  YH_REQUIRE(capacity >= 0, "capacity=%d", capacity);
+  LayerTab lt;
+  int rc = build_layer_tab(layers, L, 1, nullptr, &lt);
+  if (rc) return rc;
+  YH_REQUIRE(lt.N <= ws->max_instances, "instances %d > workspace max %lld", lt.N,
+             (long long)ws->max_instances);
+  AssignTab t;
+  t.L = L;
+  t.N = lt.N;
+  t.rect4 = rect4 ? 1 : 0;
+  t.thresh = anchor_scale_thresh;
+  for (int l = 0; l < L; ++l) {
+    t.H[l] = lt.H[l];
+    t.W[l] = lt.W[l];
+    t.A[l] = lt.A[l];
+    t.start[l] = lt.start[l];
+    for (int a = 0; a < lt.A[l]; ++a) {
+      t.ah[l][a] = layers[l].anchor_h[a];
+      t.aw[l][a] = layers[l].anchor_w[a];
+    }
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  YH_CUDA(cudaSetDevice(ws->device));
+  assign_slots_kernel<<<B, kAssignThreads, 0, s>>>(t, gt_dev, gt_offsets_dev, ws->slot_dist,
+                                                   ws->slot_gt, ws->img_count);
+  YH_LAUNCHED();
+  assign_emit_kernel<<<B, kAssignThreads, 0, s>>>(
+      t.N, B, gt_dev, gt_offsets_dev, ws->slot_gt, ws->img_count, (long long*)out_batch,
+      (long long*)out_flat, out_gt, out_target, (long long*)out_class, out_M_dev, capacity,
+      ws->err_flag);
+  YH_LAUNCHED();
+  return YH_OK;
+}

@@ -1,0 +1,165 @@
+// common.cuh — shared definitions of the yolohot kernels (sm_100a).
+//
+// Everything here is device-side plumbing: the layer table handed to kernels by value,
+// the workspace, the one decode routine every kernel shares (so that boxes decoded by
+// yh_decode, by the loss and by the NMS candidate filter are bit-identical), and
+// warp/block reduction helpers.  The library is compiled with -fmad=false: the
+// reference's arithmetic is a chain of separate ATen ops (no fused multiply-add), and
+// index decisions (NMS keeps, matcher winners) must not depend on contraction.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "yolohot.h"
+
+namespace yh {
+
+// ---------------------------------------------------------------------------------
+// errors / launch accounting
+// ---------------------------------------------------------------------------------
+void set_error(const char* fmt, ...);
+int64_t& launch_counter();
+
+#define YH_CUDA(expr)                                                                   \
+  do {                                                                                  \
+    cudaError_t _e = (expr);                                                            \
+    if (_e != cudaSuccess) {                                                            \
+      yh::set_error("%s failed at %s:%d: %s", #expr, __FILE__, __LINE__,                \
+                    cudaGetErrorString(_e));                                            \
+      return YH_ERR_CUDA;                                                               \
+    }                                                                                   \
+  } while (0)
+
+#define YH_REQUIRE(cond, ...)                                                           \
+  do {                                                                                  \
+    if (!(cond)) {                                                                      \
+      yh::set_error(__VA_ARGS__);                                                       \
+      return YH_ERR_INVALID;                                                            \
+    }                                                                                   \
+  } while (0)
+
+// after every <<<>>>: count it and surface launch-configuration errors
+#define YH_LAUNCHED()                                                                   \
+  do {                                                                                  \
+    yh::launch_counter()++;                                                             \
+    YH_CUDA(cudaGetLastError());                                                        \
+  } while (0)
+
+// ---------------------------------------------------------------------------------
+// layer table (kernel parameter, by value)
+// ---------------------------------------------------------------------------------
+struct LayerTab {
+  int L;
+  int N;                               // sum_l A*H*W
+  int C;                               // classes
+  int E;                               // 5 + C
+  int H[YH_MAX_LAYERS], W[YH_MAX_LAYERS], A[YH_MAX_LAYERS], HW[YH_MAX_LAYERS];
+  int start[YH_MAX_LAYERS];            // flat_start
+  float ah[YH_MAX_LAYERS][YH_MAX_ANCHORS];  // anchors cast to f32 (detect_2d.rs:203-209)
+  float aw[YH_MAX_LAYERS][YH_MAX_ANCHORS];
+  const float* head[YH_MAX_LAYERS];    // [B, A*E, H, W]
+};
+
+// Validates the layers and fills tab (host). heads may be NULL (then tab.head is NULL).
+int build_layer_tab(const YhLayer* layers, int L, int C, const float* const* heads,
+                    LayerTab* tab);
+
+// Position of a flat instance index inside its layer.
+struct Cell {
+  int layer, anchor, row, col, cell;  // cell = row*W + col
+};
+
+__device__ __forceinline__ Cell locate(const LayerTab& t, int flat) {
+  Cell c;
+  int l = 0;
+#pragma unroll
+  for (int i = 1; i < YH_MAX_LAYERS; ++i)
+    if (i < t.L && flat >= t.start[i]) l = i;
+  int rem = flat - t.start[l];
+  c.layer = l;
+  c.anchor = rem / t.HW[l];
+  c.cell = rem - c.anchor * t.HW[l];
+  c.row = c.cell / t.W[l];
+  c.col = c.cell - c.row * t.W[l];
+  return c;
+}
+
+// Offset (in floats) of entry 0 of (b, anchor, cell) inside head tensor of layer l;
+// entry e lives at + e * A * HW  (channel = e*A + anchor, detect_2d.rs:66).
+__device__ __forceinline__ size_t head_offset(const LayerTab& t, int l, int b, int anchor,
+                                              int cell) {
+  return ((size_t)b * (size_t)(t.A[l] * t.E) + (size_t)anchor) * (size_t)t.HW[l] + (size_t)cell;
+}
+
+// ---------------------------------------------------------------------------------
+// decode (detect_2d.rs:69-72,122-133), f32, op order of the ATen chain
+// ---------------------------------------------------------------------------------
+__device__ __forceinline__ float sigmoid_f(float x) { return 1.0f / (1.0f + expf(-x)); }
+
+__device__ __forceinline__ float decode_center(float sig, int idx, float size) {
+  // (sigmoid*2 - 0.5)/size + arange(size)[idx]/size
+  return (sig * 2.0f - 0.5f) / size + (float)idx / size;
+}
+
+__device__ __forceinline__ float decode_size(float sig, float anchor) {
+  float t = sig * 2.0f;
+  return (t * t) * anchor;
+}
+
+// ---------------------------------------------------------------------------------
+// reductions
+// ---------------------------------------------------------------------------------
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+__device__ __forceinline__ double warp_sum_d(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// streaming stores / loads: the head gradient is written once and never re-read by us
+__device__ __forceinline__ void st_stream4(float4* p, float4 v) { __stcs(p, v); }
+__device__ __forceinline__ void st_stream1(float* p, float v) { __stcs(p, v); }
+
+}  // namespace yh
+
+// ---------------------------------------------------------------------------------
+// workspace
+// ---------------------------------------------------------------------------------
+struct YhWorkspace {
+  int device;
+  int max_batch;
+  int64_t max_instances;
+  int cand_per_image;
+  int num_sms;
+
+  // assignment (assign.cu): per (image, flat) slot
+  unsigned long long* slot_dist;  // [max_batch * max_instances] f64 bits of best dist^2
+  int* slot_gt;                   // [max_batch * max_instances] winning GT (local index)
+  int* img_count;                 // [max_batch] matches per image
+
+  // loss (loss.cu)
+  double* partials;               // [YH_PARTIALS_MAX * 4]
+  unsigned int* ticket;           // last-block-done counter
+
+  // nms (nms.cu)
+  unsigned long long* cand_key;   // [max_batch * cand_per_image]
+  unsigned long long* cand_key_alt;  // sort double buffer (big path)
+  int* cand_count;                // [max_batch]
+  unsigned long long* kept_key;   // [max_batch * cand_per_image]
+  float4* kept_box;               // [max_batch * cand_per_image]
+  int* kept_count;                // [max_batch]
+  void* sort_tmp;                 // cub temp storage (big path)
+  size_t sort_tmp_bytes;
+  int* pick_flags;                // [max_batch * cand_per_image]
+
+  int* err_flag;                  // device: sticky overflow flag
+  int32_t* host_counts;           // pinned, [max_batch + 8]
+};
+
+#define YH_PARTIALS_MAX 4096

@@ -1,0 +1,190 @@
+// ffi.cu — workspace, error string, counters: the non-kernel part of the C ABI.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+#include "common.cuh"
+
+namespace yh {
+
+static thread_local char g_err[512] = "";
+static thread_local int64_t g_launches = 0;
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int64_t& launch_counter() { return g_launches; }
+
+int build_layer_tab(const YhLayer* layers, int L, int C, const float* const* heads,
+                    LayerTab* tab) {
+  YH_REQUIRE(layers != nullptr, "layers is NULL");
+  YH_REQUIRE(L >= 1 && L <= YH_MAX_LAYERS, "L=%d outside 1..%d", L, YH_MAX_LAYERS);
+  YH_REQUIRE(C >= 1, "num_classes=%d must be >= 1", C);
+  memset(tab, 0, sizeof(*tab));
+  tab->L = L;
+  tab->C = C;
+  tab->E = 5 + C;
+  int64_t expect = 0;
+  for (int l = 0; l < L; ++l) {
+    const YhLayer& y = layers[l];
+    YH_REQUIRE(y.H > 0 && y.W > 0, "layer %d: feature size %dx%d", l, y.H, y.W);
+    YH_REQUIRE(y.A >= 1 && y.A <= YH_MAX_ANCHORS, "layer %d: A=%d outside 1..%d", l, y.A,
+               YH_MAX_ANCHORS);
+    // flat ranges are consecutive (merged_dense_detection.rs:68-72)
+    YH_REQUIRE(y.flat_start == expect, "layer %d: flat_start=%lld, expected %lld", l,
+               (long long)y.flat_start, (long long)expect);
+    expect += (int64_t)y.A * y.H * y.W;
+    YH_REQUIRE(expect < (int64_t)1 << 31, "too many instances");
+    tab->H[l] = y.H;
+    tab->W[l] = y.W;
+    tab->A[l] = y.A;
+    tab->HW[l] = y.H * y.W;
+    tab->start[l] = (int)y.flat_start;
+    for (int a = 0; a < y.A; ++a) {
+      tab->ah[l][a] = (float)y.anchor_h[a];
+      tab->aw[l][a] = (float)y.anchor_w[a];
+    }
+    if (heads) {
+      YH_REQUIRE(heads[l] != nullptr, "heads[%d] is NULL", l);
+      tab->head[l] = heads[l];
+    }
+  }
+  tab->N = (int)expect;
+  return YH_OK;
+}
+
+}  // namespace yh
+
+extern "C" {
+
+const char* yh_last_error(void) { return yh::g_err; }
+
+const char* yh_version(void) { return "yolohot 0.1 (sm_100a)"; }
+
+int64_t yh_launch_count(int reset) {
+  int64_t v = yh::g_launches;
+  if (reset) yh::g_launches = 0;
+  return v;
+}
+
+int yh_workspace_destroy(YhWorkspace* ws) {
+  if (!ws) return YH_OK;
+  cudaSetDevice(ws->device);
+  cudaFree(ws->slot_dist);
+  cudaFree(ws->slot_gt);
+  cudaFree(ws->img_count);
+  cudaFree(ws->partials);
+  cudaFree(ws->ticket);
+  cudaFree(ws->cand_key);
+  cudaFree(ws->cand_key_alt);
+  cudaFree(ws->cand_count);
+  cudaFree(ws->kept_key);
+  cudaFree(ws->kept_box);
+  cudaFree(ws->kept_count);
+  cudaFree(ws->sort_tmp);
+  cudaFree(ws->pick_flags);
+  cudaFree(ws->err_flag);
+  if (ws->host_counts) cudaFreeHost(ws->host_counts);
+  delete ws;
+  return YH_OK;
+}
+
+int yh_workspace_create(int device, int max_batch, int64_t max_instances, int cand_per_image,
+                        YhWorkspace** out) {
+  YH_REQUIRE(out != nullptr, "out is NULL");
+  *out = nullptr;
+  YH_REQUIRE(max_batch >= 1, "max_batch=%d", max_batch);
+  YH_REQUIRE(max_instances >= 1 && max_instances < ((int64_t)1 << 31), "max_instances=%lld",
+             (long long)max_instances);
+  YH_REQUIRE(cand_per_image >= 1, "cand_per_image=%d", cand_per_image);
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0) {
+    yh::set_error("no CUDA device (%s); yolohot has no CPU fallback",
+                  e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+    cudaGetLastError();
+    return YH_ERR_CUDA;
+  }
+  YH_REQUIRE(device >= 0 && device < count, "device=%d outside 0..%d", device, count - 1);
+  YH_CUDA(cudaSetDevice(device));
+
+  YhWorkspace* ws = new YhWorkspace();
+  memset(ws, 0, sizeof(*ws));
+  ws->device = device;
+  ws->max_batch = max_batch;
+  ws->max_instances = max_instances;
+  ws->cand_per_image = cand_per_image;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) {
+    delete ws;
+    yh::set_error("cudaGetDeviceProperties failed");
+    return YH_ERR_CUDA;
+  }
+  ws->num_sms = prop.multiProcessorCount;
+
+  size_t slots = (size_t)max_batch * (size_t)max_instances;
+  size_t cands = (size_t)max_batch * (size_t)cand_per_image;
+#define YH_ALLOC(ptr, bytes)                                                            \
+  do {                                                                                  \
+    cudaError_t _e = cudaMalloc((void**)&(ptr), (bytes));                               \
+    if (_e != cudaSuccess) {                                                            \
+      yh::set_error("cudaMalloc(%zu) for %s failed: %s", (size_t)(bytes), #ptr,         \
+                    cudaGetErrorString(_e));                                            \
+      yh_workspace_destroy(ws);                                                         \
+      return YH_ERR_CUDA;                                                               \
+    }                                                                                   \
+  } while (0)
+  YH_ALLOC(ws->slot_dist, slots * sizeof(unsigned long long));
+  YH_ALLOC(ws->slot_gt, slots * sizeof(int));
+  YH_ALLOC(ws->img_count, (size_t)max_batch * sizeof(int));
+  YH_ALLOC(ws->partials, (size_t)YH_PARTIALS_MAX * 4 * sizeof(double));
+  YH_ALLOC(ws->ticket, 64);
+  YH_ALLOC(ws->cand_key, cands * sizeof(unsigned long long));
+  YH_ALLOC(ws->cand_key_alt, cands * sizeof(unsigned long long));
+  YH_ALLOC(ws->cand_count, (size_t)max_batch * sizeof(int));
+  YH_ALLOC(ws->kept_key, cands * sizeof(unsigned long long));
+  YH_ALLOC(ws->kept_box, cands * sizeof(float4));
+  YH_ALLOC(ws->kept_count, (size_t)max_batch * sizeof(int));
+  YH_ALLOC(ws->pick_flags, cands * sizeof(int));
+  YH_ALLOC(ws->err_flag, 64);
+#undef YH_ALLOC
+  if (cudaMemset(ws->ticket, 0, 64) != cudaSuccess ||
+      cudaMemset(ws->err_flag, 0, 64) != cudaSuccess ||
+      cudaMallocHost((void**)&ws->host_counts, ((size_t)max_batch + 8) * sizeof(int32_t)) !=
+          cudaSuccess) {
+    yh::set_error("workspace init failed: %s", cudaGetErrorString(cudaGetLastError()));
+    yh_workspace_destroy(ws);
+    return YH_ERR_CUDA;
+  }
+  *out = ws;
+  return YH_OK;
+}
+
+int yh_read_counts(YhWorkspace* ws, const int32_t* M_dev, int32_t* M_host, const int32_t* K_dev,
+                   int32_t* K_host, void* stream) {
+  YH_REQUIRE(ws != nullptr, "workspace is NULL");
+  cudaStream_t s = (cudaStream_t)stream;
+  YH_CUDA(cudaSetDevice(ws->device));
+  int32_t* h = ws->host_counts;
+  h[0] = h[1] = h[2] = 0;
+  if (M_dev) YH_CUDA(cudaMemcpyAsync(&h[0], M_dev, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+  if (K_dev) YH_CUDA(cudaMemcpyAsync(&h[1], K_dev, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+  YH_CUDA(cudaMemcpyAsync(&h[2], ws->err_flag, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+  YH_CUDA(cudaMemsetAsync(ws->err_flag, 0, sizeof(int32_t), s));
+  YH_CUDA(cudaStreamSynchronize(s));
+  if (M_host) *M_host = h[0];
+  if (K_host) *K_host = h[1];
+  if (h[2] != 0) {
+    yh::set_error("a device buffer overflowed (flag=%d): 1=matches, 2=nms candidates, "
+                  "4=nms outputs",
+                  h[2]);
+    return YH_ERR_CAPACITY;
+  }
+  return YH_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,528 @@
+// loss.cu — K4 (dense objectness BCE forward+backward, writes the whole head gradient) and
+// K3 (matched rows: box metric + class BCE forward+backward, objectness correction), i.e.
+// YoloLoss::forward (yolo-dl/src/loss/loss_.rs:227-468) plus what total_loss.backward()
+// delivers to the three head tensors (train/src/train/single_gpu.rs:161-168).
+//
+// Decomposition.  The objectness target is zero everywhere except at the M matched cells
+// (loss_.rs:393-415), so the dense pass treats EVERY cell as target 0:
+//     BCE(x, 0) = softplus(x),   d/dx = sigmoid(x)
+// and the row pass, which runs after it on the same stream, corrects the M matched cells:
+//     BCE(x, t) - BCE(x, 0) = -t*x + (lw-1)*softplus(-x),  lw = 1 + (pos_weight-1)*t
+// and overwrites their objectness gradient.  No dense target plane is ever materialised
+// (the reference builds zeros_like + index_put_, then reads both planes).
+//
+// K4 traffic: reads the obj plane (4 B/instance), writes the head gradient (4*(5+C)
+// B/instance, zeros outside the obj channels) = the 344*N bytes/image of SURVEY.md §8d.
+// It is a pure streaming kernel: float4 stores over the flat gradient tensor of each layer
+// (the tensor is contiguous, so the flat view is 16-byte aligned even for 19x19 maps whose
+// channel rows are not).
+// K3: one warp per matched row, lanes across the C class channels; the 5+C logits of a row
+// are (5+C) scattered 4-byte reads, M is small (10..15 per GT box).
+//
+// Reductions are deterministic: per-CTA partials in fixed slots, summed in a fixed order by
+// the last CTA of K3 (ticket counter), in f64.
+#include <math.h>
+
+#include "common.cuh"
+
+namespace yh {
+
+constexpr int kDenseThreads = 256;
+constexpr int kRowThreads = 256;
+constexpr int kPartHalf = YH_PARTIALS_MAX / 2;  // K4 partials in [0,kPartHalf), K3 after
+
+struct GradTab {
+  float* grad[YH_MAX_LAYERS];
+};
+
+struct LossParams {
+  int B;
+  int metric;
+  int reduction;       // YhReduction
+  float w_iou, w_cls, w_obj;
+  float cls_pos, cls_neg;   // 1-0.5*s, 1-pos (loss_.rs:326-327), cast to f32 by Tensor::full
+  float obj_base, obj_coef; // 1-s_o, s_o (loss_.rs:397-406)
+  int has_pw;
+  float pw;
+};
+
+__device__ __forceinline__ float softplus_f(float x) {
+  // log(1 + exp(x)) = max(x,0) + log1p(exp(-|x|))
+  return fmaxf(x, 0.0f) + log1pf(expf(-fabsf(x)));
+}
+
+// ---------------------------------------------------------------------------------
+// K4
+// ---------------------------------------------------------------------------------
+template <bool GRAD>
+__global__ void __launch_bounds__(kDenseThreads)
+loss_dense_kernel(const LayerTab t, const GradTab g, const int B, const float inv_numel_scale_w,
+                  const float numel, const float w_obj, const int reduction,
+                  double* __restrict__ partials) {
+  // work space: per layer, float4 quads (GRAD) or obj elements (!GRAD)
+  long long prefix[YH_MAX_LAYERS + 1];
+  prefix[0] = 0;
+#pragma unroll
+  for (int l = 0; l < YH_MAX_LAYERS; ++l) {
+    long long n = 0;
+    if (l < t.L) {
+      n = GRAD ? ((long long)B * t.A[l] * t.E * t.HW[l] + 3) / 4
+               : (long long)B * t.A[l] * t.HW[l];
+    }
+    prefix[l + 1] = prefix[l] + n;
+  }
+  const long long total = prefix[YH_MAX_LAYERS];
+  const long long stride = (long long)gridDim.x * kDenseThreads;
+  double acc = 0.0;
+  (void)inv_numel_scale_w;
+
+  for (long long i = (long long)blockIdx.x * kDenseThreads + threadIdx.x; i < total; i += stride) {
+    int l = 0;
+#pragma unroll
+    for (int k = 1; k < YH_MAX_LAYERS; ++k)
+      if (k < t.L && i >= prefix[k]) l = k;
+    const long long li = i - prefix[l];
+    const int run = t.A[l] * t.HW[l];                 // floats per entry per image
+    const long long per_img = (long long)run * t.E;   // floats per image
+    const float* __restrict__ head = t.head[l];
+    if (GRAD) {
+      const long long len = (long long)B * per_img;
+      const long long idx = li * 4;
+      // offset inside the image; 32-bit modulo whenever the layer tensor allows it
+      const long long r = (len < (1LL << 32))
+                              ? (long long)((unsigned)idx % (unsigned)per_img)
+                              : idx % per_img;
+      float* gp = g.grad[l] + idx;
+      const bool full = idx + 3 < len;
+      // obj channels of an image: [4*run, 5*run)
+      const bool touches = (r + 3 >= 4LL * run) && (r < 5LL * run);
+      if (full && !touches) {
+        st_stream4(reinterpret_cast<float4*>(gp), make_float4(0.f, 0.f, 0.f, 0.f));
+      } else {
+        float v[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          if (idx + k < len) {
+            long long rk = r + k;
+            if (rk >= per_img) rk -= per_img;
+            if (rk >= 4LL * run && rk < 5LL * run) {
+              const float x = __ldcs(head + idx + k);
+              acc += (double)softplus_f(x);
+              // BCE backward, target 0: sigmoid(x) [/numel for Mean] * upstream w_obj
+              float gi = sigmoid_f(x);
+              if (reduction == YH_REDUCTION_MEAN) gi = gi / numel;
+              v[k] = gi * w_obj;
+            }
+          }
+        }
+        if (full) {
+          st_stream4(reinterpret_cast<float4*>(gp), make_float4(v[0], v[1], v[2], v[3]));
+        } else {
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            if (idx + k < len) st_stream1(gp + k, v[k]);
+        }
+      }
+    } else {
+      const long long b = li / run;
+      const long long j = li - b * run;
+      const float x = __ldcs(head + b * per_img + 4LL * run + j);
+      acc += (double)softplus_f(x);
+    }
+  }
+
+  // CTA partial, fixed slot
+  __shared__ double s_part[kDenseThreads / 32];
+  acc = warp_sum_d(acc);
+  if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double tot = 0.0;
+#pragma unroll
+    for (int k = 0; k < kDenseThreads / 32; ++k) tot += s_part[k];
+    partials[(size_t)blockIdx.x * 4] = tot;
+  }
+}
+
+// ---------------------------------------------------------------------------------
+// box metric, forward + reverse-mode gradient of the same op sequence
+// (tch-goodies/src/compound_tensor/cycxhw.rs:67-120, tlbr.rs:81-134,214-225)
+// ---------------------------------------------------------------------------------
+// ATen's maximum/minimum backward: all of the gradient to the selected operand, half on ties
+__device__ __forceinline__ float w_gt(float a, float b) { return a > b ? 1.f : (a == b ? 0.5f : 0.f); }
+__device__ __forceinline__ float w_lt(float a, float b) { return a < b ? 1.f : (a == b ? 0.5f : 0.f); }
+
+struct Box4 {
+  float cy, cx, h, w;
+};
+
+// Returns the metric; if want_grad, d receives d(metric)/d(pred) * g.
+__device__ __forceinline__ float box_metric(const int metric, const Box4 p, const Box4 q,
+                                            const float g, const bool want_grad, Box4& d) {
+  const float EPS = 1e-16f;  // utils.rs:5 (f64 1e-16 added to an f32 tensor)
+  // TLBR (tlbr.rs:214-225)
+  const float pt = p.cy - p.h / 2.0f, pb = p.cy + p.h / 2.0f;
+  const float pl = p.cx - p.w / 2.0f, pr = p.cx + p.w / 2.0f;
+  const float qt = q.cy - q.h / 2.0f, qb = q.cy + q.h / 2.0f;
+  const float ql = q.cx - q.w / 2.0f, qr = q.cx + q.w / 2.0f;
+  // intersection (tlbr.rs:81-108)
+  const float max_t = fmaxf(pt, qt), max_l = fmaxf(pl, ql);
+  const float min_b = fminf(pb, qb), min_r = fminf(pr, qr);
+  const float dhh = min_b - max_t, dww = min_r - max_l;
+  const float ih = fmaxf(dhh, 0.0f), iw = fmaxf(dww, 0.0f);
+  const float inter = ih * iw;
+  const float ap = p.h * p.w, aq = q.h * q.w;
+  const float outer = ap + aq - inter + EPS;
+  const float iou = inter / outer;
+
+  float m = iou;
+  // closure (tlbr.rs:111-134)
+  const float ct = fminf(pt, qt), cl = fminf(pl, ql), cb = fmaxf(pb, qb), cr = fmaxf(pr, qr);
+  const float ch = cb - ct, cw = cr - cl;
+  float carea = 0.f, gu = 0.f, gv = 0.f, diag = 0.f, cdist = 0.f, qd = 0.f;
+  float dy = 0.f, dx = 0.f, ang_p = 0.f, ang_q = 0.f, shape = 0.f, alpha = 0.f;
+  const float PI2 = (float)(3.14159265358979323846 * 3.14159265358979323846);
+  if (metric == YH_METRIC_GIOU) {
+    carea = ch * cw;
+    gu = carea - outer;
+    gv = carea + EPS;
+    m = iou - gu / gv;
+  } else if (metric == YH_METRIC_DIOU || metric == YH_METRIC_CIOU) {
+    diag = ch * ch + cw * cw + EPS;
+    dy = p.cy - q.cy;
+    dx = p.cx - q.cx;
+    cdist = dy * dy + dx * dx;
+    qd = cdist / diag;
+    m = iou - qd;
+    if (metric == YH_METRIC_CIOU) {
+      ang_p = atan2f(p.h, p.w);
+      ang_q = atan2f(q.h, q.w);
+      const float da = ang_p - ang_q;
+      shape = (da * da) * 4.0f / PI2;
+      alpha = shape / (1.0f - iou + shape);  // no_grad (cycxhw.rs:117)
+      m = iou - qd + alpha * shape;          // '+' as in the reference (cycxhw.rs:119)
+    }
+  }
+  if (!want_grad) return m;
+
+  float d_pcy = 0.f, d_pcx = 0.f, d_ph = 0.f, d_pw = 0.f;
+  float d_pt = 0.f, d_pb = 0.f, d_pl = 0.f, d_pr = 0.f;
+  float d_iou = g;
+  float d_outer = 0.f;
+  float d_ch = 0.f, d_cw = 0.f;
+  if (metric == YH_METRIC_GIOU) {
+    // m = iou - gu/gv
+    const float d_gu = -g / gv;
+    const float d_gv = g * (gu / gv) / gv;
+    const float d_carea = d_gu + d_gv;
+    d_outer += -d_gu;
+    d_ch += d_carea * cw;
+    d_cw += d_carea * ch;
+  } else if (metric == YH_METRIC_DIOU || metric == YH_METRIC_CIOU) {
+    const float d_cdist = -g / diag;
+    const float d_diag = g * (cdist / diag) / diag;
+    d_ch += d_diag * (2.0f * ch);
+    d_cw += d_diag * (2.0f * cw);
+    d_pcy += d_cdist * (2.0f * dy);
+    d_pcx += d_cdist * (2.0f * dx);
+    if (metric == YH_METRIC_CIOU) {
+      const float d_shape = g * alpha;
+      const float d_ang = d_shape / PI2 * 4.0f * (2.0f * (ang_p - ang_q));
+      const float rec = 1.0f / (p.h * p.h + p.w * p.w);  // atan2 backward
+      d_ph += d_ang * p.w * rec;
+      d_pw += d_ang * (-p.h) * rec;
+    }
+  }
+  // closure edges
+  d_pb += d_ch * w_gt(pb, qb);
+  d_pt += -d_ch * w_lt(pt, qt);
+  d_pr += d_cw * w_gt(pr, qr);
+  d_pl += -d_cw * w_lt(pl, ql);
+  // iou = inter / outer
+  float d_inter = d_iou / outer;
+  d_outer += -d_iou * (inter / outer) / outer;
+  // outer = ap + aq - inter + eps
+  const float d_ap = d_outer;
+  d_inter += -d_outer;
+  d_ph += d_ap * p.w;
+  d_pw += d_ap * p.h;
+  // inter = ih * iw, clamp_min backward passes where the input >= 0
+  const float d_ih = d_inter * iw, d_iw = d_inter * ih;
+  const float d_dhh = dhh >= 0.0f ? d_ih : 0.0f;
+  const float d_dww = dww >= 0.0f ? d_iw : 0.0f;
+  d_pb += d_dhh * w_lt(pb, qb);
+  d_pt += -d_dhh * w_gt(pt, qt);
+  d_pr += d_dww * w_lt(pr, qr);
+  d_pl += -d_dww * w_gt(pl, ql);
+  // pt = cy - h/2 ...
+  d_pcy += d_pt + d_pb;
+  d_ph += (d_pb - d_pt) / 2.0f;
+  d_pcx += d_pl + d_pr;
+  d_pw += (d_pr - d_pl) / 2.0f;
+  d.cy = d_pcy;
+  d.cx = d_pcx;
+  d.h = d_ph;
+  d.w = d_pw;
+  return m;
+}
+
+// ---------------------------------------------------------------------------------
+// K3
+// ---------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kRowThreads)
+loss_rows_kernel(const LayerTab t, const GradTab g, const LossParams p,
+                 const long long* __restrict__ m_batch, const long long* __restrict__ m_flat,
+                 const float* __restrict__ m_target, const long long* __restrict__ m_class,
+                 const int* __restrict__ M_dev, const int capacity,
+                 float* __restrict__ iou_score, float* __restrict__ pred_rows,
+                 double* __restrict__ partials, const int n_dense_partials,
+                 unsigned int* __restrict__ ticket, float* __restrict__ losses4) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int warps = kRowThreads / 32;
+  const int M = min(*M_dev, capacity);
+  const bool want_grad = g.grad[0] != nullptr;
+  const float Mf = (float)M;
+  const float MCf = (float)((long long)M * t.C);
+  const float numel_obj = (float)((long long)p.B * t.N);
+
+  double a_iou = 0.0, a_cls = 0.0, a_obj = 0.0;  // lane 0 of each warp accumulates
+
+  for (int m = blockIdx.x * warps + wid; m < M; m += gridDim.x * warps) {
+    const int b = (int)m_batch[m];
+    const int flat = (int)m_flat[m];
+    const Cell c = locate(t, flat);
+    const int l = c.layer;
+    const size_t es = (size_t)t.A[l] * (size_t)t.HW[l];
+    const size_t off = head_offset(t, l, b, c.anchor, c.cell);
+    const float* hp = t.head[l] + off;
+    float* gp = want_grad ? g.grad[l] + off : nullptr;
+
+    // the five leading logits (same address across the warp: one broadcast transaction each)
+    const float x0 = hp[0], x1 = hp[es], x2 = hp[2 * es], x3 = hp[3 * es], xo = hp[4 * es];
+    const float s0 = sigmoid_f(x0), s1 = sigmoid_f(x1), s2 = sigmoid_f(x2), s3 = sigmoid_f(x3);
+    Box4 pb;
+    pb.cy = decode_center(s0, c.row, (float)t.H[l]);
+    pb.cx = decode_center(s1, c.col, (float)t.W[l]);
+    pb.h = decode_size(s2, t.ah[l][c.anchor]);
+    pb.w = decode_size(s3, t.aw[l][c.anchor]);
+    Box4 tb;
+    tb.cy = m_target[(size_t)m * 4 + 0];
+    tb.cx = m_target[(size_t)m * 4 + 1];
+    tb.h = m_target[(size_t)m * 4 + 2];
+    tb.w = m_target[(size_t)m * 4 + 3];
+
+    // d total / d metric: total = w_iou * mean(1 - metric)
+    float gm = p.w_iou;
+    if (p.reduction == YH_REDUCTION_MEAN) gm = gm / Mf;
+    gm = -gm;
+    Box4 d = {0.f, 0.f, 0.f, 0.f};
+    const float metric = box_metric(p.metric, pb, tb, gm, want_grad, d);
+
+    // class BCE over C channels, lanes strided
+    const int cls = (int)m_class[m];
+    float bce = 0.f;
+    for (int k = lane; k < t.C; k += 32) {
+      const float x = hp[(size_t)(5 + k) * es];
+      const float tt = (k == cls) ? p.cls_pos : p.cls_neg;
+      bce += (1.0f - tt) * x + softplus_f(-x);
+      if (want_grad) {
+        float gi = sigmoid_f(x) - tt;
+        if (p.reduction == YH_REDUCTION_MEAN) gi = gi / MCf;
+        gp[(size_t)(5 + k) * es] = gi * p.w_cls;
+      }
+      if (pred_rows) pred_rows[(size_t)m * t.E + 5 + k] = x;
+    }
+    bce = warp_sum(bce);
+
+    if (lane == 0) {
+      a_iou += (double)(1.0f - metric);
+      a_cls += (double)bce;
+      // objectness target at this cell (loss_.rs:397-406)
+      float to = p.obj_base + fminf(fmaxf(metric, 0.0f), 1.0f) * p.obj_coef;
+      const float lwm1 = p.has_pw ? (p.pw - 1.0f) * to : 0.0f;
+      a_obj += (double)(-to * xo) + (double)(lwm1 * softplus_f(-xo));
+      if (iou_score) iou_score[m] = metric;
+      if (pred_rows) {
+        float* r = pred_rows + (size_t)m * t.E;
+        r[0] = pb.cy; r[1] = pb.cx; r[2] = pb.h; r[3] = pb.w; r[4] = xo;
+      }
+      if (want_grad) {
+        // chain through the decode (detect_2d.rs:69-72,122-133):
+        //   cy = (2s-0.5)/H + off  -> dcy/ds = 2/H ; s' = s(1-s)
+        //   h  = (2s)^2 * a        -> dh/ds  = a * 2*(2s) * 2
+        const float Hf = (float)t.H[l], Wf = (float)t.W[l];
+        gp[0] = (d.cy / Hf * 2.0f) * ((1.0f - s0) * s0);
+        gp[es] = (d.cx / Wf * 2.0f) * ((1.0f - s1) * s1);
+        gp[2 * es] = ((d.h * t.ah[l][c.anchor]) * (2.0f * (s2 * 2.0f)) * 2.0f) * ((1.0f - s2) * s2);
+        gp[3 * es] = ((d.w * t.aw[l][c.anchor]) * (2.0f * (s3 * 2.0f)) * 2.0f) * ((1.0f - s3) * s3);
+        // objectness gradient with the real target (overwrites K4's target-0 value)
+        const float so = sigmoid_f(xo);
+        float gi;
+        if (p.has_pw) {
+          const float tp = p.pw * to;
+          gi = ((tp + 1.0f) - to) * so - tp;
+        } else {
+          gi = so - to;
+        }
+        if (p.reduction == YH_REDUCTION_MEAN) gi = gi / numel_obj;
+        gp[4 * es] = gi * p.w_obj;
+      }
+    }
+  }
+
+  // CTA partials -> fixed slot
+  __shared__ double s_acc[kRowThreads / 32][3];
+  __shared__ bool s_last;
+  if (lane == 0) {
+    s_acc[wid][0] = a_iou;
+    s_acc[wid][1] = a_cls;
+    s_acc[wid][2] = a_obj;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double s[3] = {0.0, 0.0, 0.0};
+    for (int k = 0; k < warps; ++k) {
+      s[0] += s_acc[k][0];
+      s[1] += s_acc[k][1];
+      s[2] += s_acc[k][2];
+    }
+    double* dst = partials + (size_t)(kPartHalf + blockIdx.x) * 4;
+    dst[0] = s[0];
+    dst[1] = s[1];
+    dst[2] = s[2];
+    __threadfence();
+    const unsigned int prev = atomicAdd(ticket, 1u);
+    s_last = (prev == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!s_last) return;
+
+  // last CTA: fixed-order final sums
+  __threadfence();
+  __shared__ double s_red[kRowThreads][4];
+  double r[4] = {0.0, 0.0, 0.0, 0.0};
+  for (int i = threadIdx.x; i < n_dense_partials; i += kRowThreads)
+    r[3] += __ldcg(&partials[(size_t)i * 4]);
+  for (int i = threadIdx.x; i < (int)gridDim.x; i += kRowThreads) {
+    const double* src = partials + (size_t)(kPartHalf + i) * 4;
+    r[0] += __ldcg(&src[0]);
+    r[1] += __ldcg(&src[1]);
+    r[2] += __ldcg(&src[2]);
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k) s_red[threadIdx.x][k] = r[k];
+  __syncthreads();
+  for (int o = kRowThreads / 2; o > 0; o >>= 1) {
+    if (threadIdx.x < o) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) s_red[threadIdx.x][k] += s_red[threadIdx.x + o][k];
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    double iou_sum = s_red[0][0], cls_sum = s_red[0][1];
+    double obj_sum = s_red[0][3] + s_red[0][2];
+    float iou_l, cls_l, obj_l;
+    if (p.reduction == YH_REDUCTION_MEAN) {
+      // empty inputs give 0 (loss_.rs:309-314, bce_with_logits_loss.rs:74-77)
+      iou_l = M > 0 ? (float)(iou_sum / (double)M) : 0.0f;
+      cls_l = M > 0 ? (float)(cls_sum / ((double)M * (double)t.C)) : 0.0f;
+      obj_l = (float)(obj_sum / ((double)p.B * (double)t.N));
+    } else {
+      iou_l = (float)iou_sum;
+      cls_l = (float)cls_sum;
+      obj_l = (float)obj_sum;
+    }
+    // loss_.rs:258-260, f32 tensor arithmetic with f32-cast scalars
+    const float total = p.w_iou * iou_l + p.w_cls * cls_l + p.w_obj * obj_l;
+    losses4[0] = total;
+    losses4[1] = iou_l;
+    losses4[2] = cls_l;
+    losses4[3] = obj_l;
+    *ticket = 0u;  // ready for the next call on this stream
+  }
+}
+
+}  // namespace yh
+
+extern "C" int yh_loss_fwd_bwd(YhWorkspace* ws, const float* const* heads, const YhLayer* layers,
+                               int L, int B, int C, const int64_t* m_batch, const int64_t* m_flat,
+                               const float* m_target, const int64_t* m_class,
+                               const int32_t* M_dev, int capacity, const YhLossCfg* cfg,
+                               float* losses4_dev, float* iou_score_dev, float* pred_rows_dev,
+                               float* const* grad_heads, void* stream) {
+  using namespace yh;
+  YH_REQUIRE(ws != nullptr, "workspace is NULL");
+  YH_REQUIRE(cfg != nullptr && losses4_dev != nullptr && M_dev != nullptr, "NULL argument");
+  YH_REQUIRE(capacity == 0 || (m_batch && m_flat && m_target && m_class), "match list is NULL");
+  YH_REQUIRE(B >= 1 && B <= ws->max_batch, "B=%d outside 1..max_batch=%d", B, ws->max_batch);
+  LayerTab tab;
+  int rc = build_layer_tab(layers, L, C, heads, &tab);
+  if (rc) return rc;
+  // YoloLossInit::build validation (loss_.rs:64-87)
+  YH_REQUIRE(cfg->smooth_classification_coef >= 0.0 && cfg->smooth_classification_coef <= 1.0,
+             "smooth_classification_coef must be in range [0, 1]");
+  YH_REQUIRE(cfg->smooth_objectness_coef >= 0.0 && cfg->smooth_objectness_coef <= 1.0,
+             "smooth_objectness_coef must be in range [0, 1]");
+  YH_REQUIRE(cfg->iou_loss_weight >= 0.0, "iou_loss_weight must be non-negative");
+  YH_REQUIRE(cfg->objectness_loss_weight >= 0.0, "objectness_loss_weight must be non-negative");
+  YH_REQUIRE(cfg->classification_loss_weight >= 0.0,
+             "classification_loss_weight must be non-negative");
+  YH_REQUIRE(cfg->reduction == YH_REDUCTION_MEAN || cfg->reduction == YH_REDUCTION_SUM,
+             "reduction %d is not supported", cfg->reduction);
+  if (cfg->box_metric == YH_METRIC_HAUSDORFF) {
+    set_error("box_metric Hausdorff is outside the accelerated path (DESIGN.md, out of scope)");
+    return YH_ERR_UNSUPPORTED;
+  }
+  YH_REQUIRE(cfg->box_metric >= YH_METRIC_IOU && cfg->box_metric <= YH_METRIC_CIOU,
+             "box_metric=%d", cfg->box_metric);
+
+  GradTab g;
+  memset(&g, 0, sizeof(g));
+  if (grad_heads) {
+    for (int l = 0; l < L; ++l) {
+      YH_REQUIRE(grad_heads[l] != nullptr, "grad_heads[%d] is NULL", l);
+      YH_REQUIRE(((uintptr_t)grad_heads[l] & 15) == 0, "grad_heads[%d] not 16-byte aligned", l);
+      g.grad[l] = grad_heads[l];
+    }
+  }
+  LossParams p;
+  p.B = B;
+  p.metric = cfg->box_metric;
+  p.reduction = cfg->reduction;
+  p.w_iou = (float)cfg->iou_loss_weight;
+  p.w_cls = (float)cfg->classification_loss_weight;
+  p.w_obj = (float)cfg->objectness_loss_weight;
+  const double pos = 1.0 - 0.5 * cfg->smooth_classification_coef;
+  p.cls_pos = (float)pos;
+  p.cls_neg = (float)(1.0 - pos);
+  p.obj_base = (float)(1.0 - cfg->smooth_objectness_coef);
+  p.obj_coef = (float)cfg->smooth_objectness_coef;
+  p.has_pw = cfg->has_objectness_pos_weight ? 1 : 0;
+  p.pw = (float)cfg->objectness_pos_weight;
+
+  cudaStream_t s = (cudaStream_t)stream;
+  YH_CUDA(cudaSetDevice(ws->device));
+  const float numel = (float)((long long)B * tab.N);
+  int dense_grid = ws->num_sms * 8;
+  if (dense_grid > kPartHalf) dense_grid = kPartHalf;
+  if (grad_heads) {
+    loss_dense_kernel<true><<<dense_grid, kDenseThreads, 0, s>>>(
+        tab, g, B, 0.f, numel, p.w_obj, p.reduction, ws->partials);
+  } else {
+    loss_dense_kernel<false><<<dense_grid, kDenseThreads, 0, s>>>(
+        tab, g, B, 0.f, numel, p.w_obj, p.reduction, ws->partials);
+  }
+  YH_LAUNCHED();
+  int row_grid = ws->num_sms * 2;
+  const int need = (capacity + (kRowThreads / 32) - 1) / (kRowThreads / 32);
+  if (row_grid > need) row_grid = need;
+  if (row_grid < 1) row_grid = 1;
+  if (row_grid > kPartHalf) row_grid = kPartHalf;
+  loss_rows_kernel<<<row_grid, kRowThreads, 0, s>>>(
+      tab, g, p, (const long long*)m_batch, (const long long*)m_flat, m_target,
+      (const long long*)m_class, M_dev, capacity, iou_score_dev, pred_rows_dev, ws->partials,
+      dense_grid, ws->ticket, losses4_dev);
+  YH_LAUNCHED();
+  return YH_OK;
+}
