@@ -152,18 +152,33 @@ int yh_loss_fwd_bwd(YhWorkspace* ws, const float* const* heads, const YhLayer* l
  * grouped greedy NMS of tch_nms::nms_by_scores (call site nms.rs:142-148).
  * conf = sigmoid(obj)*sigmoid(cls); candidates: sigmoid(obj) >= thr && conf >= thr (f32
  * compare, nms.rs:97-99); group = batch (by_class=0) or batch*C+class (nms.rs:129-133).
+ * Greedy rule (oracle/nms.py, the stand-in for the un-vendored tch-nms): candidates in
+ * score-descending order, equal scores in nonzero() order (class*N+instance ascending); a
+ * candidate is dropped iff a kept box of its group has IoU > iou_threshold.  NMS is global per
+ * image: the reference's 65536-row chunking (nms.rs:135-151) is NOT reproduced.
  * Kept rows are emitted ordered by (batch, score desc, class*N+instance asc):
  *   kb/kc/ki  i64 batches/classes/instances ; tlbr [cap,4] f32 (t,l,b,r) ; conf [cap]
- *   out_K_dev int32 count (device).
- * SYNCHRONISES the stream once (candidate counts, as `nonzero` does at nms.rs:100). */
+ *   out_K_dev int32 count (device), clamped to capacity (overflow -> yh_read_counts error).
+ * Does not synchronise. */
 int yh_nms(YhWorkspace* ws, const float* const* heads, const YhLayer* layers, int L, int B,
            int C, double confidence_threshold, double iou_threshold, int suppress_by_class,
            int64_t* kb, int64_t* kc, int64_t* ki, float* tlbr, float* conf,
            int32_t* out_K_dev, int capacity, void* stream);
 
+/* ---- a13 alone: drop-in for `tch_nms::nms_by_scores(ltrb, scores, groups, iou_thr)`
+ * (external crate tch-nms @138b5e40, call site `yolo-dl/src/loss/nms.rs:142-148`).
+ *   ltrb [K,4] f32 (l,t,r,b) 16-byte aligned ; scores [K] f32 ; groups [K] i64
+ *   keep [K] i64: kept row indices, score-descending (ties: lower row first)
+ *   out_K_dev int32 count (device).
+ * K is limited by the workspace: next_pow2(K) <= max_batch * next_pow2(cand_per_image). */
+int yh_nms_by_scores(YhWorkspace* ws, const float* ltrb, const float* scores,
+                     const int64_t* groups, int K, double iou_threshold, int64_t* keep,
+                     int32_t* out_K_dev, void* stream);
+
 /* ---- a14: YoloInference::forward post-pass (`yolo-dl/src/loss/inference.rs:50-77`):
  * among kept rows of the same (batch, instance) keep the one with max confidence.
- * In-place compaction of the yh_nms outputs; *io_K_dev updated. */
+ * max_by_key keeps the LAST maximum: equal confidences keep the later row.
+ * In-place, order-preserving compaction of the yh_nms outputs; *io_K_dev updated. */
 int yh_inference_pick(YhWorkspace* ws, int64_t* kb, int64_t* kc, int64_t* ki, float* tlbr,
                       float* conf, int32_t* io_K_dev, int capacity, void* stream);
 

@@ -147,16 +147,14 @@ struct YhWorkspace {
   double* partials;               // [YH_PARTIALS_MAX * 4]
   unsigned int* ticket;           // last-block-done counter
 
-  // nms (nms.cu)
-  unsigned long long* cand_key;   // [max_batch * cand_per_image]
-  unsigned long long* cand_key_alt;  // sort double buffer (big path)
+  // nms (nms.cu): per-image regions of cand_stride (= next pow2 of cand_per_image) entries
+  long long cand_stride;
+  unsigned long long* cand_key;   // [max_batch * cand_stride] (~score bits << 32 | index)
   int* cand_count;                // [max_batch]
-  unsigned long long* kept_key;   // [max_batch * cand_per_image]
-  float4* kept_box;               // [max_batch * cand_per_image]
+  unsigned long long* kept_key;   // [max_batch * cand_stride]
+  float4* kept_box;               // [max_batch * cand_stride] (t,l,b,r)
+  long long* kept_grp;            // [max_batch * cand_stride] suppression group of a kept box
   int* kept_count;                // [max_batch]
-  void* sort_tmp;                 // cub temp storage (big path)
-  size_t sort_tmp_bytes;
-  int* pick_flags;                // [max_batch * cand_per_image]
 
   int* err_flag;                  // device: sticky overflow flag
   int32_t* host_counts;           // pinned, [max_batch + 8]

@@ -80,13 +80,11 @@ int yh_workspace_destroy(YhWorkspace* ws) {
   cudaFree(ws->partials);
   cudaFree(ws->ticket);
   cudaFree(ws->cand_key);
-  cudaFree(ws->cand_key_alt);
   cudaFree(ws->cand_count);
   cudaFree(ws->kept_key);
   cudaFree(ws->kept_box);
   cudaFree(ws->kept_count);
-  cudaFree(ws->sort_tmp);
-  cudaFree(ws->pick_flags);
+  cudaFree(ws->kept_grp);
   cudaFree(ws->err_flag);
   if (ws->host_counts) cudaFreeHost(ws->host_counts);
   delete ws;
@@ -127,7 +125,9 @@ int yh_workspace_create(int device, int max_batch, int64_t max_instances, int ca
   ws->num_sms = prop.multiProcessorCount;
 
   size_t slots = (size_t)max_batch * (size_t)max_instances;
-  size_t cands = (size_t)max_batch * (size_t)cand_per_image;
+  ws->cand_stride = 2;
+  while (ws->cand_stride < cand_per_image) ws->cand_stride <<= 1;
+  size_t cands = (size_t)max_batch * (size_t)ws->cand_stride;
 #define YH_ALLOC(ptr, bytes)                                                            \
   do {                                                                                  \
     cudaError_t _e = cudaMalloc((void**)&(ptr), (bytes));                               \
@@ -144,12 +144,11 @@ int yh_workspace_create(int device, int max_batch, int64_t max_instances, int ca
   YH_ALLOC(ws->partials, (size_t)YH_PARTIALS_MAX * 4 * sizeof(double));
   YH_ALLOC(ws->ticket, 64);
   YH_ALLOC(ws->cand_key, cands * sizeof(unsigned long long));
-  YH_ALLOC(ws->cand_key_alt, cands * sizeof(unsigned long long));
   YH_ALLOC(ws->cand_count, (size_t)max_batch * sizeof(int));
   YH_ALLOC(ws->kept_key, cands * sizeof(unsigned long long));
   YH_ALLOC(ws->kept_box, cands * sizeof(float4));
   YH_ALLOC(ws->kept_count, (size_t)max_batch * sizeof(int));
-  YH_ALLOC(ws->pick_flags, cands * sizeof(int));
+  YH_ALLOC(ws->kept_grp, cands * sizeof(long long));
   YH_ALLOC(ws->err_flag, 64);
 #undef YH_ALLOC
   if (cudaMemset(ws->ticket, 0, 64) != cudaSuccess ||

@@ -1,0 +1,617 @@
+// nms.cu — K5: candidate filter + grouped greedy NMS + post-NMS class pick.
+//   NonMaxSuppression::forward   yolo-dl/src/loss/nms.rs:72-170
+//   tch_nms::nms_by_scores       external (call site nms.rs:142-148); semantics restated in
+//                                oracle/nms.py: greedy, score-descending, equal scores keep the
+//                                lower index, suppress iff IoU > thr, IoU = inter/(a+b-inter)
+//   YoloInference::forward       yolo-dl/src/loss/inference.rs:50-77 (class pick)
+//
+// Pipeline of yh_nms (3 launches):
+//   nms_filter_kernel   one warp per 32 instances.  Reads the objectness plane (4 B/instance);
+//                       only where sigmoid(obj) >= thr — conf = obj*cls <= obj, so nothing else
+//                       can pass (nms.rs:97-99) — the warp reads that instance's C class logits
+//                       together (lane = class), ballots conf >= thr and appends 64-bit keys
+//                       (~ordered(score) << 32 | class*N + instance) to the image's candidate
+//                       list with ONE atomicAdd per ballot.  The [B,C,N] confidence tensor of
+//                       the reference is never materialised.
+//   nms_segment_kernel  one CTA per image: sorts the keys (bitonic; in shared memory up to 8192
+//                       keys, hybrid shared/global above), so the list is in score-descending,
+//                       then nonzero()-index-ascending order, and runs the greedy pass in tiles
+//                       of 1024 candidates: each thread tests its candidate against the kept
+//                       list (shared-memory cache, warp-broadcast reads), then warps resolve
+//                       their 32 candidates in order with ballot/shuffle and publish the newly
+//                       kept boxes to the later warps.  No K x K mask exists anywhere.
+//                       Per-class suppression only adds "same class" to the predicate, so one
+//                       sorted list per image serves both modes (nms.rs:129-133).
+//   nms_emit_kernel     ordered compaction of the per-image kept lists into the outputs.
+// yh_nms_by_scores exposes the same engine on explicit [K,4] ltrb boxes / scores / int64 groups,
+// i.e. the drop-in for tch_nms::nms_by_scores itself.
+#include <math.h>
+
+#include "common.cuh"
+
+namespace yh {
+
+constexpr int kFilterThreads = 256;
+constexpr int kNmsThreads = 1024;
+constexpr int kSortTile = 8192;    // keys sorted in shared memory at once (64 KB)
+constexpr int kKeptCache = 2048;   // kept boxes cached in shared memory (aliases the sort tile)
+
+// ---------------------------------------------------------------------------------
+// keys
+// ---------------------------------------------------------------------------------
+// order-preserving float -> uint (ascending), inverted so that ascending keys = descending score
+__device__ __forceinline__ unsigned score_to_bits(float s) {
+  unsigned u = __float_as_uint(s);
+  u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+  return ~u;
+}
+__device__ __forceinline__ float bits_to_score(unsigned k) {
+  unsigned u = ~k;
+  u = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
+  return __uint_as_float(u);
+}
+__device__ __forceinline__ unsigned long long make_key(float score, unsigned idx) {
+  return ((unsigned long long)score_to_bits(score) << 32) | (unsigned long long)idx;
+}
+
+// ---------------------------------------------------------------------------------
+// box providers: key index -> (t,l,b,r) box and suppression group
+// ---------------------------------------------------------------------------------
+struct HeadBoxes {
+  LayerTab t;
+  int by_class;
+  // idx = class*N + instance (nonzero() order inside an image, nms.rs:100-103)
+  __device__ __forceinline__ void get(int seg, unsigned idx, float4& box, long long& grp) const {
+    const int cls = (int)(idx / (unsigned)t.N);
+    const int n = (int)(idx - (unsigned)cls * (unsigned)t.N);
+    const Cell c = locate(t, n);
+    const int l = c.layer;
+    const size_t es = (size_t)t.A[l] * (size_t)t.HW[l];
+    const float* hp = t.head[l] + head_offset(t, l, seg, c.anchor, c.cell);
+    const float cy = decode_center(sigmoid_f(__ldg(hp)), c.row, (float)t.H[l]);
+    const float cx = decode_center(sigmoid_f(__ldg(hp + es)), c.col, (float)t.W[l]);
+    const float h = decode_size(sigmoid_f(__ldg(hp + 2 * es)), t.ah[l][c.anchor]);
+    const float w = decode_size(sigmoid_f(__ldg(hp + 3 * es)), t.aw[l][c.anchor]);
+    // nms.rs:91-94
+    box.x = cy - h / 2.0f;  // t
+    box.y = cx - w / 2.0f;  // l
+    box.z = cy + h / 2.0f;  // b
+    box.w = cx + w / 2.0f;  // r
+    grp = by_class ? (long long)cls : 0ll;
+  }
+};
+
+struct ArrayBoxes {
+  const float* ltrb;        // [K,4] l,t,r,b (nms.rs:128)
+  const long long* groups;  // [K]
+  __device__ __forceinline__ void get(int, unsigned idx, float4& box, long long& grp) const {
+    const float4 v = __ldg(reinterpret_cast<const float4*>(ltrb) + idx);
+    box.x = v.y;
+    box.y = v.x;
+    box.z = v.w;
+    box.w = v.z;
+    grp = __ldg(groups + idx);
+  }
+};
+
+// IoU > thr, arithmetic of the greedy reference (areas first, inter/(a+b-inter), f32; the
+// comparison promotes to the f64 threshold the caller passes, nms.rs:146)
+__device__ __forceinline__ float box_area(const float4 a) { return (a.w - a.y) * (a.z - a.x); }
+
+__device__ __forceinline__ bool suppresses(const float4 a, const float area_a, const float4 c,
+                                           const float area_c, const double thr) {
+  const float xx1 = fmaxf(a.y, c.y), yy1 = fmaxf(a.x, c.x);
+  const float xx2 = fminf(a.w, c.w), yy2 = fminf(a.z, c.z);
+  const float w = fmaxf(0.0f, xx2 - xx1), h = fmaxf(0.0f, yy2 - yy1);
+  const float inter = w * h;
+  const float ovr = inter / (area_a + area_c - inter);
+  return (double)ovr > thr;
+}
+
+// ---------------------------------------------------------------------------------
+// candidate filter (heads -> per-image key lists)
+// ---------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kFilterThreads)
+nms_filter_kernel(const LayerTab t, const float thr, unsigned long long* __restrict__ keys,
+                  const int stride, const int cap, int* __restrict__ count,
+                  int* __restrict__ err_flag) {
+  const int b = blockIdx.y;
+  const int lane = threadIdx.x & 31;
+  const int n = blockIdx.x * kFilterThreads + threadIdx.x;
+  const bool valid = n < t.N;
+  const float* hp = nullptr;
+  unsigned es = 0;
+  float so = 0.0f;
+  if (valid) {
+    const Cell c = locate(t, n);
+    es = (unsigned)(t.A[c.layer] * t.HW[c.layer]);
+    hp = t.head[c.layer] + head_offset(t, c.layer, b, c.anchor, c.cell);
+    so = sigmoid_f(__ldg(hp + 4 * (size_t)es));
+  }
+  unsigned m = __ballot_sync(0xffffffffu, valid && so >= thr);
+  unsigned long long* out = keys + (size_t)b * (size_t)stride;
+  while (m) {
+    const int src = __ffs(m) - 1;
+    m &= m - 1;
+    const float* hp_s = (const float*)__shfl_sync(0xffffffffu, (unsigned long long)hp, src);
+    const unsigned es_s = __shfl_sync(0xffffffffu, es, src);
+    const float so_s = __shfl_sync(0xffffffffu, so, src);
+    const int n_s = __shfl_sync(0xffffffffu, n, src);
+    for (int k0 = 0; k0 < t.C; k0 += 32) {
+      const int k = k0 + lane;
+      bool hit = false;
+      float conf = 0.0f;
+      if (k < t.C) {
+        conf = so_s * sigmoid_f(__ldg(hp_s + (size_t)(5 + k) * es_s));
+        hit = conf >= thr;
+      }
+      const unsigned hm = __ballot_sync(0xffffffffu, hit);
+      if (hm) {
+        int base = 0;
+        if (lane == 0) base = atomicAdd(&count[b], __popc(hm));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (hit) {
+          const int pos = base + __popc(hm & ((1u << lane) - 1u));
+          if (pos < cap)
+            out[pos] = make_key(conf, (unsigned)k * (unsigned)t.N + (unsigned)n_s);
+          else
+            atomicOr(err_flag, 2);
+        }
+      }
+    }
+  }
+}
+
+// explicit scores -> keys of one segment
+__global__ void nms_pack_kernel(const float* __restrict__ scores, const int K,
+                                unsigned long long* __restrict__ keys, int* __restrict__ count) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < K) keys[i] = make_key(scores[i], (unsigned)i);
+  if (i == 0) count[0] = K;
+}
+
+// ---------------------------------------------------------------------------------
+// bitonic sort, one CTA
+// ---------------------------------------------------------------------------------
+// compare-exchange passes j = j_hi .. 1 of merge size k over n (pow2) keys in shared memory;
+// gbase = global index of s[0] (the direction of a pair depends on the global index)
+__device__ __forceinline__ void smem_passes(unsigned long long* s, const int n, const int gbase,
+                                            const int k, const int j_hi) {
+  for (int j = j_hi; j >= 1; j >>= 1) {
+    for (int p = threadIdx.x; p < n / 2; p += kNmsThreads) {
+      const int i = ((p & ~(j - 1)) << 1) | (p & (j - 1));
+      const int l = i | j;
+      const bool asc = ((gbase + i) & k) == 0;
+      const unsigned long long a = s[i], c = s[l];
+      if ((a > c) == asc) {
+        s[i] = c;
+        s[l] = a;
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// sorts keys[0..K) ascending in place; keys has room for next_pow2(K) entries
+__device__ void sort_keys(unsigned long long* __restrict__ keys, const int K,
+                          unsigned long long* s) {
+  if (K <= 1) return;
+  int P = 2;
+  while (P < K) P <<= 1;
+  if (P <= kSortTile) {
+    for (int i = threadIdx.x; i < P; i += kNmsThreads) s[i] = (i < K) ? keys[i] : ~0ull;
+    __syncthreads();
+    for (int k = 2; k <= P; k <<= 1) smem_passes(s, P, 0, k, k >> 1);
+    for (int i = threadIdx.x; i < K; i += kNmsThreads) keys[i] = s[i];
+    __syncthreads();
+    return;
+  }
+  // hybrid: tiles of kSortTile in shared memory, wider strides through global memory (L2)
+  for (int i = K + threadIdx.x; i < P; i += kNmsThreads) keys[i] = ~0ull;
+  __syncthreads();
+  for (int base = 0; base < P; base += kSortTile) {
+    for (int i = threadIdx.x; i < kSortTile; i += kNmsThreads) s[i] = keys[base + i];
+    __syncthreads();
+    for (int k = 2; k <= kSortTile; k <<= 1) smem_passes(s, kSortTile, base, k, k >> 1);
+    for (int i = threadIdx.x; i < kSortTile; i += kNmsThreads) keys[base + i] = s[i];
+    __syncthreads();
+  }
+  for (int k = kSortTile * 2; k <= P; k <<= 1) {
+    for (int j = k >> 1; j >= kSortTile; j >>= 1) {
+      for (int p = threadIdx.x; p < P / 2; p += kNmsThreads) {
+        const int i = ((p & ~(j - 1)) << 1) | (p & (j - 1));
+        const int l = i | j;
+        const bool asc = (i & k) == 0;
+        const unsigned long long a = keys[i], c = keys[l];
+        if ((a > c) == asc) {
+          keys[i] = c;
+          keys[l] = a;
+        }
+      }
+      __syncthreads();
+    }
+    for (int base = 0; base < P; base += kSortTile) {
+      for (int i = threadIdx.x; i < kSortTile; i += kNmsThreads) s[i] = keys[base + i];
+      __syncthreads();
+      smem_passes(s, kSortTile, base, k, kSortTile >> 1);
+      for (int i = threadIdx.x; i < kSortTile; i += kNmsThreads) keys[base + i] = s[i];
+      __syncthreads();
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------
+// sort + greedy NMS, one CTA per segment
+// ---------------------------------------------------------------------------------
+struct SegView {
+  unsigned long long* keys;      // [S * stride]
+  unsigned long long* kept_key;  // [S * stride]
+  float4* kept_box;              // [S * stride]
+  long long* kept_grp;           // [S * stride]
+  int* count;                    // [S] candidates (may exceed cap: clamped)
+  int* kept_count;               // [S]
+  long long stride;
+  int cap;
+};
+
+template <class P>
+__global__ void __launch_bounds__(kNmsThreads)
+nms_segment_kernel(const P prov, const SegView v, const double iou_thr) {
+  extern __shared__ __align__(16) unsigned long long s_keys[];
+  __shared__ unsigned s_alive[kNmsThreads / 32];
+  __shared__ float4 s_stage_box[32];
+  __shared__ long long s_stage_grp[32];
+  __shared__ int s_nstage;
+
+  const int seg = blockIdx.x;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int K = min(v.count[seg], v.cap);
+  unsigned long long* keys = v.keys + (size_t)seg * (size_t)v.stride;
+  unsigned long long* kept_key = v.kept_key + (size_t)seg * (size_t)v.stride;
+  float4* kept_box = v.kept_box + (size_t)seg * (size_t)v.stride;
+  long long* kept_grp = v.kept_grp + (size_t)seg * (size_t)v.stride;
+
+  sort_keys(keys, K, s_keys);
+  __syncthreads();
+
+  // the sort tile becomes the kept-box cache
+  float4* c_box = reinterpret_cast<float4*>(s_keys);
+  long long* c_grp = reinterpret_cast<long long*>(c_box + kKeptCache);
+  int nkept = 0;
+
+  for (int base = 0; base < K; base += kNmsThreads) {
+    const int i = base + threadIdx.x;
+    bool alive = i < K;
+    unsigned long long key = 0;
+    float4 box = make_float4(0.f, 0.f, 0.f, 0.f);
+    long long grp = 0;
+    float area = 0.f;
+    if (alive) {
+      key = keys[i];
+      prov.get(seg, (unsigned)(key & 0xffffffffull), box, grp);
+      area = box_area(box);
+      // against everything kept by earlier tiles
+      const int nc = min(nkept, kKeptCache);
+      for (int q = 0; q < nc; ++q) {
+        const float4 kb = c_box[q];
+        if (c_grp[q] == grp && suppresses(kb, box_area(kb), box, area, iou_thr)) {
+          alive = false;
+          break;
+        }
+      }
+      if (alive) {
+        for (int q = kKeptCache; q < nkept; ++q) {
+          const float4 kb = kept_box[q];
+          if (kept_grp[q] == grp && suppresses(kb, box_area(kb), box, area, iou_thr)) {
+            alive = false;
+            break;
+          }
+        }
+      }
+    }
+    {
+      const unsigned am = __ballot_sync(0xffffffffu, alive);
+      if (lane == 0) s_alive[wid] = am;
+    }
+    __syncthreads();
+
+    const int rounds = min(kNmsThreads / 32, (K - base + 31) / 32);
+    for (int s = 0; s < rounds; ++s) {
+      if (s_alive[s] == 0u) continue;  // block-uniform
+      if (wid == s) {
+        // in-order resolution of this warp's 32 candidates
+        unsigned m = s_alive[s];
+        unsigned keepm = 0u;
+        while (m) {
+          const int j = __ffs(m) - 1;
+          keepm |= 1u << j;
+          float4 bj;
+          bj.x = __shfl_sync(0xffffffffu, box.x, j);
+          bj.y = __shfl_sync(0xffffffffu, box.y, j);
+          bj.z = __shfl_sync(0xffffffffu, box.z, j);
+          bj.w = __shfl_sync(0xffffffffu, box.w, j);
+          const long long gj = __shfl_sync(0xffffffffu, grp, j);
+          if (alive && lane > j && gj == grp && suppresses(bj, box_area(bj), box, area, iou_thr))
+            alive = false;
+          m = __ballot_sync(0xffffffffu, alive) & ~((2u << j) - 1u);
+        }
+        if ((keepm >> lane) & 1u) {
+          const int r = __popc(keepm & ((1u << lane) - 1u));
+          const int pos = nkept + r;
+          kept_key[pos] = key;
+          kept_box[pos] = box;
+          kept_grp[pos] = grp;
+          if (pos < kKeptCache) {
+            c_box[pos] = box;
+            c_grp[pos] = grp;
+          }
+          s_stage_box[r] = box;
+          s_stage_grp[r] = grp;
+        }
+        if (lane == 0) s_nstage = __popc(keepm);
+        alive = false;  // resolved
+      }
+      __syncthreads();
+      const int ns = s_nstage;
+      if (wid > s) {
+        if (alive) {
+          for (int q = 0; q < ns; ++q) {
+            const float4 kb = s_stage_box[q];
+            if (s_stage_grp[q] == grp && suppresses(kb, box_area(kb), box, area, iou_thr)) {
+              alive = false;
+              break;
+            }
+          }
+        }
+        const unsigned am = __ballot_sync(0xffffffffu, alive);
+        if (lane == 0) s_alive[wid] = am;
+      }
+      nkept += ns;
+      __syncthreads();
+    }
+    __syncthreads();  // s_alive is rewritten by the next tile
+  }
+  if (threadIdx.x == 0) v.kept_count[seg] = nkept;
+}
+
+// ---------------------------------------------------------------------------------
+// ordered compaction of the kept lists
+// ---------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+nms_emit_kernel(const SegView v, const int S, const int N, long long* __restrict__ kb,
+                long long* __restrict__ kc, long long* __restrict__ ki, float* __restrict__ tlbr,
+                float* __restrict__ conf, long long* __restrict__ keep_idx,
+                int* __restrict__ out_K, const int capacity, int* __restrict__ err_flag) {
+  __shared__ int s_warp[8];
+  __shared__ int s_base;
+  const int seg = blockIdx.x;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  int part = 0;
+  for (int i = threadIdx.x; i < seg; i += 256) part += v.kept_count[i];
+  for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+  if (lane == 0) s_warp[wid] = part;
+  __syncthreads();
+  const int mine = v.kept_count[seg];
+  if (threadIdx.x == 0) {
+    int tot = 0;
+    for (int i = 0; i < 8; ++i) tot += s_warp[i];
+    s_base = tot;
+    if (seg == S - 1) {
+      const int total = tot + mine;
+      *out_K = min(total, capacity);
+      if (total > capacity) atomicOr(err_flag, 4);
+    }
+  }
+  __syncthreads();
+  const int base = s_base;
+  const unsigned long long* kk = v.kept_key + (size_t)seg * (size_t)v.stride;
+  const float4* bx = v.kept_box + (size_t)seg * (size_t)v.stride;
+  for (int r = threadIdx.x; r < mine; r += 256) {
+    const int pos = base + r;
+    if (pos >= capacity) break;
+    const unsigned long long key = kk[r];
+    const unsigned idx = (unsigned)(key & 0xffffffffull);
+    if (keep_idx) {
+      keep_idx[pos] = (long long)idx;
+    } else {
+      const unsigned cls = idx / (unsigned)N;
+      kb[pos] = seg;
+      kc[pos] = (long long)cls;
+      ki[pos] = (long long)(idx - cls * (unsigned)N);
+      reinterpret_cast<float4*>(tlbr)[pos] = bx[r];
+      conf[pos] = bits_to_score((unsigned)(key >> 32));
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------
+// YoloInference class pick (inference.rs:50-77): among kept rows of one (batch, instance)
+// keep the max-confidence one; max_by_key keeps the LAST maximum, i.e. the highest row.
+// One CTA: slot table init -> atomicMax -> ordered in-place compaction.
+// ---------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kNmsThreads)
+pick_kernel(long long* __restrict__ kb, long long* __restrict__ kc, long long* __restrict__ ki,
+            float* __restrict__ tlbr, float* __restrict__ conf, int* __restrict__ io_K,
+            const int capacity, unsigned long long* __restrict__ slot, const int max_batch,
+            const long long max_instances) {
+  __shared__ int s_warp[kNmsThreads / 32];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int K = min(*io_K, capacity);
+  for (int i = threadIdx.x; i < K; i += kNmsThreads) {
+    const long long b = kb[i], n = ki[i];
+    if (b >= 0 && b < max_batch && n >= 0 && n < max_instances) slot[b * max_instances + n] = 0ull;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < K; i += kNmsThreads) {
+    const long long b = kb[i], n = ki[i];
+    if (b >= 0 && b < max_batch && n >= 0 && n < max_instances)
+      atomicMax(&slot[b * max_instances + n],
+                ((unsigned long long)__float_as_uint(conf[i]) << 32) | (unsigned)i);
+  }
+  __syncthreads();
+  int base = 0;
+  for (int tile = 0; tile < K; tile += kNmsThreads) {
+    const int i = tile + threadIdx.x;
+    bool keep = false;
+    long long b = 0, c = 0, n = 0;
+    float4 box = make_float4(0.f, 0.f, 0.f, 0.f);
+    float cf = 0.f;
+    if (i < K) {
+      b = kb[i];
+      c = kc[i];
+      n = ki[i];
+      box = reinterpret_cast<const float4*>(tlbr)[i];
+      cf = conf[i];
+      const bool in = b >= 0 && b < max_batch && n >= 0 && n < max_instances;
+      keep = !in || slot[b * max_instances + n] ==
+                        (((unsigned long long)__float_as_uint(cf) << 32) | (unsigned)i);
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, keep);
+    if (lane == 0) s_warp[wid] = __popc(m);
+    __syncthreads();
+    int before = 0, total = 0;
+#pragma unroll
+    for (int k = 0; k < kNmsThreads / 32; ++k) {
+      const int cnt = s_warp[k];
+      if (k < wid) before += cnt;
+      total += cnt;
+    }
+    if (keep) {
+      const int pos = base + before + __popc(m & ((1u << lane) - 1u));
+      kb[pos] = b;
+      kc[pos] = c;
+      ki[pos] = n;
+      reinterpret_cast<float4*>(tlbr)[pos] = box;
+      conf[pos] = cf;
+    }
+    base += total;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *io_K = base;
+}
+
+static int next_pow2(long long x) {
+  long long p = 1;
+  while (p < x) p <<= 1;
+  return (int)p;
+}
+
+template <class P>
+static int launch_segments(const P& prov, const SegView& v, int S, double iou_thr, cudaStream_t s) {
+  static bool attr_set = false;  // idempotent; a race only repeats the call
+  const size_t smem = (size_t)kSortTile * sizeof(unsigned long long);
+  if (!attr_set) {
+    YH_CUDA(cudaFuncSetAttribute(nms_segment_kernel<P>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)smem));
+    attr_set = true;
+  }
+  nms_segment_kernel<P><<<S, kNmsThreads, smem, s>>>(prov, v, iou_thr);
+  YH_LAUNCHED();
+  return YH_OK;
+}
+
+static SegView make_view(YhWorkspace* ws) {
+  SegView v;
+  v.keys = ws->cand_key;
+  v.kept_key = ws->kept_key;
+  v.kept_box = ws->kept_box;
+  v.kept_grp = ws->kept_grp;
+  v.count = ws->cand_count;
+  v.kept_count = ws->kept_count;
+  v.stride = ws->cand_stride;
+  v.cap = ws->cand_per_image;
+  return v;
+}
+
+}  // namespace yh
+
+extern "C" {
+
+int yh_nms(YhWorkspace* ws, const float* const* heads, const YhLayer* layers, int L, int B, int C,
+           double confidence_threshold, double iou_threshold, int suppress_by_class, int64_t* kb,
+           int64_t* kc, int64_t* ki, float* tlbr, float* conf, int32_t* out_K_dev, int capacity,
+           void* stream) {
+  using namespace yh;
+  YH_REQUIRE(ws != nullptr, "workspace is NULL");
+  YH_REQUIRE(heads != nullptr, "heads is NULL");
+  YH_REQUIRE(kb && kc && ki && tlbr && conf && out_K_dev, "output pointer is NULL");
+  YH_REQUIRE(((uintptr_t)tlbr & 15) == 0, "tlbr not 16-byte aligned");
+  YH_REQUIRE(B >= 1 && B <= ws->max_batch && B <= 65535, "B=%d outside 1..max_batch=%d", B,
+             ws->max_batch);
+  YH_REQUIRE(capacity >= 0, "capacity=%d", capacity);
+  // NonMaxSuppressionInit::build (nms.rs:35-39)
+  YH_REQUIRE(iou_threshold >= 0.0, "iou_threshold must be non-negative");
+  YH_REQUIRE(confidence_threshold >= 0.0, "confidence_threshold must be non-negative");
+  HeadBoxes prov;
+  int rc = build_layer_tab(layers, L, C, heads, &prov.t);
+  if (rc) return rc;
+  prov.by_class = suppress_by_class ? 1 : 0;
+  YH_REQUIRE((long long)prov.t.N * C < (1ll << 32), "C*N=%lld does not fit the 32-bit key index",
+             (long long)prov.t.N * C);
+  cudaStream_t s = (cudaStream_t)stream;
+  YH_CUDA(cudaSetDevice(ws->device));
+  YH_CUDA(cudaMemsetAsync(ws->cand_count, 0, (size_t)B * sizeof(int), s));
+  SegView v = make_view(ws);
+  dim3 grid((prov.t.N + kFilterThreads - 1) / kFilterThreads, B);
+  nms_filter_kernel<<<grid, kFilterThreads, 0, s>>>(prov.t, (float)confidence_threshold, v.keys,
+                                                    (int)v.stride, v.cap, v.count, ws->err_flag);
+  YH_LAUNCHED();
+  rc = launch_segments(prov, v, B, iou_threshold, s);
+  if (rc) return rc;
+  nms_emit_kernel<<<B, 256, 0, s>>>(v, B, prov.t.N, (long long*)kb, (long long*)kc,
+                                    (long long*)ki, tlbr, conf, nullptr, out_K_dev, capacity,
+                                    ws->err_flag);
+  YH_LAUNCHED();
+  return YH_OK;
+}
+
+int yh_nms_by_scores(YhWorkspace* ws, const float* ltrb, const float* scores,
+                     const int64_t* groups, int K, double iou_threshold, int64_t* keep,
+                     int32_t* out_K_dev, void* stream) {
+  using namespace yh;
+  YH_REQUIRE(ws != nullptr, "workspace is NULL");
+  YH_REQUIRE(K >= 0, "K=%d", K);
+  YH_REQUIRE(out_K_dev != nullptr, "out_K is NULL");
+  YH_REQUIRE(K == 0 || (ltrb && scores && groups && keep), "NULL argument");
+  YH_REQUIRE(((uintptr_t)ltrb & 15) == 0, "ltrb not 16-byte aligned");
+  const long long room = (long long)ws->max_batch * ws->cand_stride;
+  YH_REQUIRE(K == 0 || next_pow2(K) <= room, "K=%d exceeds the workspace (%lld keys)", K, room);
+  cudaStream_t s = (cudaStream_t)stream;
+  YH_CUDA(cudaSetDevice(ws->device));
+  if (K == 0) {
+    YH_CUDA(cudaMemsetAsync(out_K_dev, 0, sizeof(int32_t), s));
+    return YH_OK;
+  }
+  SegView v = make_view(ws);
+  v.stride = room;  // one segment over the whole region
+  v.cap = K;
+  nms_pack_kernel<<<(K + 255) / 256, 256, 0, s>>>(scores, K, v.keys, v.count);
+  YH_LAUNCHED();
+  ArrayBoxes prov;
+  prov.ltrb = ltrb;
+  prov.groups = (const long long*)groups;
+  int rc = launch_segments(prov, v, 1, iou_threshold, s);
+  if (rc) return rc;
+  nms_emit_kernel<<<1, 256, 0, s>>>(v, 1, 1, nullptr, nullptr, nullptr, nullptr, nullptr,
+                                    (long long*)keep, out_K_dev, K, ws->err_flag);
+  YH_LAUNCHED();
+  return YH_OK;
+}
+
+int yh_inference_pick(YhWorkspace* ws, int64_t* kb, int64_t* kc, int64_t* ki, float* tlbr,
+                      float* conf, int32_t* io_K_dev, int capacity, void* stream) {
+  using namespace yh;
+  YH_REQUIRE(ws != nullptr, "workspace is NULL");
+  YH_REQUIRE(kb && kc && ki && tlbr && conf && io_K_dev, "NULL argument");
+  YH_REQUIRE(((uintptr_t)tlbr & 15) == 0, "tlbr not 16-byte aligned");
+  YH_REQUIRE(capacity >= 0, "capacity=%d", capacity);
+  cudaStream_t s = (cudaStream_t)stream;
+  YH_CUDA(cudaSetDevice(ws->device));
+  pick_kernel<<<1, kNmsThreads, 0, s>>>((long long*)kb, (long long*)kc, (long long*)ki, tlbr, conf,
+                                        io_K_dev, capacity, ws->slot_dist, ws->max_batch,
+                                        (long long)ws->max_instances);
+  YH_LAUNCHED();
+  return YH_OK;
+}
+
+}  // extern "C"
