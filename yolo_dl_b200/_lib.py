@@ -1,0 +1,116 @@
+"""ctypes binding of libyolohot.so (the C ABI of include/yolohot.h).
+
+There is NO CPU fallback: if the shared library is missing, `load()` raises; if there is no CUDA
+device, `yh_workspace_create` fails and the error text of `yh_last_error()` is raised.
+"""
+import ctypes
+import os
+from ctypes import POINTER, c_char_p, c_double, c_float, c_int, c_int32, c_int64, c_void_p
+
+YH_MAX_LAYERS = 8
+YH_MAX_ANCHORS = 8
+
+YH_OK, YH_ERR_INVALID, YH_ERR_CUDA, YH_ERR_CAPACITY, YH_ERR_UNSUPPORTED = range(5)
+
+METRICS = {"iou": 0, "giou": 1, "diou": 2, "ciou": 3, "hausdorff": 4}
+REDUCTIONS = {"mean": 0, "sum": 1}
+
+
+class YhLayer(ctypes.Structure):
+    _fields_ = [("H", c_int32), ("W", c_int32), ("A", c_int32), ("_pad", c_int32),
+                ("flat_start", c_int64),
+                ("anchor_h", c_double * YH_MAX_ANCHORS), ("anchor_w", c_double * YH_MAX_ANCHORS)]
+
+
+class YhLossCfg(ctypes.Structure):
+    _fields_ = [("box_metric", c_int32), ("reduction", c_int32),
+                ("iou_loss_weight", c_double), ("classification_loss_weight", c_double),
+                ("objectness_loss_weight", c_double), ("smooth_classification_coef", c_double),
+                ("smooth_objectness_coef", c_double), ("has_objectness_pos_weight", c_int32),
+                ("_pad", c_int32), ("objectness_pos_weight", c_double)]
+
+
+class YoloHotError(RuntimeError):
+    def __init__(self, status, text):
+        super().__init__(f"yolohot status {status}: {text}")
+        self.status = status
+        self.text = text
+
+
+LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libyolohot.so")
+
+# every symbol include/yolohot.h declares: name -> (restype, argtypes)
+_PF = POINTER(c_void_p)
+SYMBOLS = {
+    "yh_workspace_create": (c_int, [c_int, c_int, c_int64, c_int, POINTER(c_void_p)]),
+    "yh_workspace_destroy": (c_int, [c_void_p]),
+    "yh_last_error": (c_char_p, []),
+    "yh_version": (c_char_p, []),
+    "yh_decode": (c_int, [c_void_p, c_int, c_int, POINTER(YhLayer), c_void_p, c_void_p, c_void_p,
+                          c_void_p, c_int64, c_void_p]),
+    "yh_decode_merged": (c_int, [_PF, POINTER(YhLayer), c_int, c_int, c_int, c_void_p, c_void_p,
+                                 c_void_p, c_void_p, c_int64, c_void_p]),
+    "yh_assign": (c_int, [c_void_p, c_void_p, c_void_p, c_int, POINTER(YhLayer), c_int, c_int,
+                          c_double, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                          c_int, c_void_p]),
+    "yh_loss_fwd_bwd": (c_int, [c_void_p, _PF, POINTER(YhLayer), c_int, c_int, c_int, c_void_p,
+                                c_void_p, c_void_p, c_void_p, c_void_p, c_int, POINTER(YhLossCfg),
+                                c_void_p, c_void_p, c_void_p, _PF, c_void_p]),
+    "yh_nms": (c_int, [c_void_p, _PF, POINTER(YhLayer), c_int, c_int, c_int, c_double, c_double,
+                       c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
+                       c_void_p]),
+    "yh_nms_by_scores": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_double, c_void_p,
+                                 c_void_p, c_void_p]),
+    "yh_inference_pick": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                  c_void_p, c_int, c_void_p]),
+    "yh_read_counts": (c_int, [c_void_p, c_void_p, POINTER(c_int32), c_void_p, POINTER(c_int32),
+                               c_void_p]),
+    "yh_launch_count": (c_int64, [c_int]),
+}
+
+_lib = None
+
+
+def load():
+    """Loads libyolohot.so and types every entry point.  Raises if it is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; "
+            "g.build()'` (or `make -C yolo_dl_b200/csrc`). yolohot has no CPU fallback.")
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (res, args) in SYMBOLS.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(status):
+    if status != YH_OK:
+        raise YoloHotError(status, load().yh_last_error().decode())
+
+
+def make_layers(infos):
+    """infos: sequence with .H .W .anchors [(h,w) ratio f64] .flat_start -> (YhLayer * L)."""
+    arr = (YhLayer * len(infos))()
+    for i, info in enumerate(infos):
+        if len(info.anchors) > YH_MAX_ANCHORS:
+            raise ValueError(f"layer {i}: {len(info.anchors)} anchors > {YH_MAX_ANCHORS}")
+        arr[i].H, arr[i].W, arr[i].A = info.H, info.W, len(info.anchors)
+        arr[i].flat_start = info.flat_start
+        for a, (h, w) in enumerate(info.anchors):
+            arr[i].anchor_h[a] = float(h)
+            arr[i].anchor_w[a] = float(w)
+    return arr
+
+
+def ptr_array(tensors):
+    """device pointers of a list of tensors as a `const float* const*` argument."""
+    arr = (c_void_p * len(tensors))()
+    for i, t in enumerate(tensors):
+        arr[i] = t.data_ptr()
+    return arr
