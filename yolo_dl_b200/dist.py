@@ -1,0 +1,39 @@
+"""Multi-GPU plumbing of the hot path.
+
+The path shards by image with NO data-path collective: every image's decode, assignment, loss
+terms and NMS groups are independent.  One process per GPU owns a contiguous image range, exactly
+like `forward_step`'s `narrow` (train/src/train/multi_gpu.rs:545-574).  The only exchange the
+reference performs on this path is the minibatch-weighted mean of the loss scalars
+(multi_gpu.rs:188-195, loss_.rs:527-577, tch-goodies/src/tensor.rs:66-80); here it is ONE
+all-reduce(sum) of 5 floats over NCCL (gloo in the CPU tests).
+"""
+from typing import Tuple
+
+import torch
+import torch.distributed as dist
+
+
+def shard_range(batch: int, rank: int, world: int) -> Tuple[int, int]:
+    """contiguous [start, end) of images of `rank`; sizes differ by at most one."""
+    base, rem = divmod(batch, world)
+    start = rank * base + min(rank, rem)
+    return start, start + base + (1 if rank < rem else 0)
+
+
+def weighted_mean_losses(losses4: torch.Tensor, local_batch: int, group=None) -> torch.Tensor:
+    """YoloLossOutput::weighted_mean over the ranks: sum_g loss_g * B_g / sum_g B_g.
+    `losses4` = [total, iou, classification, objectness] of this rank's LOCAL means (reference
+    behaviour: per-device means, not a global mean).  Returns the 4 combined scalars."""
+    buf = torch.empty(5, dtype=torch.float32, device=losses4.device)
+    buf[:4] = losses4.detach().float() * float(local_batch)
+    buf[4] = float(local_batch)
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=group)
+    return buf[:4] / buf[4]
+
+
+def gradient_scale(local_batch: int, global_batch: int) -> float:
+    """multi_gpu.rs:619-623,690-693: each replica's gradient is weighted by its minibatch size
+    and the sum divided by the global batch; with an all-reduce(sum) of the caller's backbone
+    gradients this is the per-rank factor."""
+    return float(local_batch) / float(global_batch)
