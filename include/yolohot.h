@@ -191,6 +191,15 @@ int yh_read_counts(YhWorkspace* ws, const int32_t* M_dev, int32_t* M_host,
  * reset (bench.py's `gpu_launches`). */
 int64_t yh_launch_count(int reset);
 
+/* Optional per-launch timing for benchmarks: while enabled (thread-local) every kernel launch of
+ * this library is bracketed by a CUDA event pair on its launch stream.  yh_timing_read
+ * synchronises on those events and returns, per kernel id (order: decode, assign_slots,
+ * assign_emit, loss_dense, loss_rows, nms_filter, nms_segment, nms_emit, nms_pack, pick), the
+ * summed device time in ms and the launch count since the last read. */
+#define YH_NUM_KERNELS 10
+int yh_timing_enable(int on);
+int yh_timing_read(double* ms_sum, int64_t* launches, int n);
+
 #ifdef __cplusplus
 }
 #endif

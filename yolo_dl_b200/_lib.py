@@ -66,7 +66,13 @@ SYMBOLS = {
     "yh_read_counts": (c_int, [c_void_p, c_void_p, POINTER(c_int32), c_void_p, POINTER(c_int32),
                                c_void_p]),
     "yh_launch_count": (c_int64, [c_int]),
+    "yh_timing_enable": (c_int, [c_int]),
+    "yh_timing_read": (c_int, [POINTER(c_double), POINTER(c_int64), c_int]),
 }
+
+KERNEL_NAMES = ["decode_kernel", "assign_slots_kernel", "assign_emit_kernel", "loss_dense_kernel",
+                "loss_rows_kernel", "nms_filter_kernel", "nms_segment_kernel", "nms_emit_kernel",
+                "nms_pack_kernel", "pick_kernel"]
 
 _lib = None
 

@@ -243,13 +243,15 @@ extern "C" int yh_assign(YhWorkspace* ws, const double* gt_dev, const int32_t* g
   }
   cudaStream_t s = (cudaStream_t)stream;
   YH_CUDA(cudaSetDevice(ws->device));
+  YH_TIME(YH_K_ASSIGN_SLOTS, s);
   assign_slots_kernel<<<B, kAssignThreads, 0, s>>>(t, gt_dev, gt_offsets_dev, ws->slot_dist,
                                                    ws->slot_gt, ws->img_count);
-  YH_LAUNCHED();
+  YH_LAUNCHED(s);
+  YH_TIME(YH_K_ASSIGN_EMIT, s);
   assign_emit_kernel<<<B, kAssignThreads, 0, s>>>(
       t.N, B, gt_dev, gt_offsets_dev, ws->slot_gt, ws->img_count, (long long*)out_batch,
       (long long*)out_flat, out_gt, out_target, (long long*)out_class, out_M_dev, capacity,
       ws->err_flag);
-  YH_LAUNCHED();
+  YH_LAUNCHED(s);
   return YH_OK;
 }

@@ -39,9 +39,20 @@ int64_t& launch_counter();
     }                                                                                   \
   } while (0)
 
+// kernel ids of the optional per-launch CUDA-event timing (yh_timing_enable / yh_timing_read)
+enum KernelId {
+  YH_K_DECODE = 0, YH_K_ASSIGN_SLOTS, YH_K_ASSIGN_EMIT, YH_K_LOSS_DENSE, YH_K_LOSS_ROWS,
+  YH_K_NMS_FILTER, YH_K_NMS_SEGMENT, YH_K_NMS_EMIT, YH_K_NMS_PACK, YH_K_PICK, YH_K_COUNT
+};
+void timing_begin(int id, cudaStream_t s);  // no-ops unless timing is enabled on this thread
+void timing_end(cudaStream_t s);
+
+// before every <<<>>>
+#define YH_TIME(id, s) yh::timing_begin(yh::id, s)
 // after every <<<>>>: count it and surface launch-configuration errors
-#define YH_LAUNCHED()                                                                   \
+#define YH_LAUNCHED(s)                                                                  \
   do {                                                                                  \
+    yh::timing_end(s);                                                                  \
     yh::launch_counter()++;                                                             \
     YH_CUDA(cudaGetLastError());                                                        \
   } while (0)

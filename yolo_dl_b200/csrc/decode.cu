@@ -115,8 +115,9 @@ static int launch_decode(const LayerTab& tab, int B, float* cy, float* cx, float
              tab.N);
   const int quads = (tab.N + 3) / 4;
   dim3 grid((quads + kDecodeThreads - 1) / kDecodeThreads, B);
+  YH_TIME(YH_K_DECODE, s);
   decode_kernel<<<grid, kDecodeThreads, 0, s>>>(tab, cy, cx, h, w, (long long)out_stride);
-  YH_LAUNCHED();
+  YH_LAUNCHED(s);
   return YH_OK;
 }
 

@@ -2,6 +2,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <vector>
 
 #include "common.cuh"
 
@@ -18,6 +19,42 @@ void set_error(const char* fmt, ...) {
 }
 
 int64_t& launch_counter() { return g_launches; }
+
+// ---- optional per-launch timing: one CUDA event pair per launch, on the launch stream ----
+struct TimedLaunch {
+  int id;
+  cudaEvent_t a, b;
+};
+static thread_local bool g_timing = false;
+static thread_local std::vector<TimedLaunch>* g_timed = nullptr;
+static thread_local std::vector<cudaEvent_t>* g_pool = nullptr;
+
+static cudaEvent_t get_event() {
+  if (g_pool && !g_pool->empty()) {
+    cudaEvent_t e = g_pool->back();
+    g_pool->pop_back();
+    return e;
+  }
+  cudaEvent_t e = nullptr;
+  cudaEventCreate(&e);
+  return e;
+}
+
+void timing_begin(int id, cudaStream_t s) {
+  if (!g_timing) return;
+  if (!g_timed) g_timed = new std::vector<TimedLaunch>();
+  TimedLaunch t;
+  t.id = id;
+  t.a = get_event();
+  t.b = get_event();
+  cudaEventRecord(t.a, s);
+  g_timed->push_back(t);
+}
+
+void timing_end(cudaStream_t s) {
+  if (!g_timing || !g_timed || g_timed->empty()) return;
+  cudaEventRecord(g_timed->back().b, s);
+}
 
 int build_layer_tab(const YhLayer* layers, int L, int C, const float* const* heads,
                     LayerTab* tab) {
@@ -69,6 +106,34 @@ int64_t yh_launch_count(int reset) {
   int64_t v = yh::g_launches;
   if (reset) yh::g_launches = 0;
   return v;
+}
+
+int yh_timing_enable(int on) {
+  yh::g_timing = on != 0;
+  return YH_OK;
+}
+
+int yh_timing_read(double* ms_sum, int64_t* launches, int n) {
+  using namespace yh;
+  for (int i = 0; i < n; ++i) {
+    if (ms_sum) ms_sum[i] = 0.0;
+    if (launches) launches[i] = 0;
+  }
+  if (!g_timed) return YH_OK;
+  if (!g_pool) g_pool = new std::vector<cudaEvent_t>();
+  for (const TimedLaunch& t : *g_timed) {
+    float ms = 0.f;
+    YH_CUDA(cudaEventSynchronize(t.b));
+    YH_CUDA(cudaEventElapsedTime(&ms, t.a, t.b));
+    if (t.id < n) {
+      if (ms_sum) ms_sum[t.id] += ms;
+      if (launches) launches[t.id] += 1;
+    }
+    g_pool->push_back(t.a);
+    g_pool->push_back(t.b);
+  }
+  g_timed->clear();
+  return YH_OK;
 }
 
 int yh_workspace_destroy(YhWorkspace* ws) {

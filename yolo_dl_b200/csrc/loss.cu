@@ -507,22 +507,25 @@ extern "C" int yh_loss_fwd_bwd(YhWorkspace* ws, const float* const* heads, const
   int dense_grid = ws->num_sms * 8;
   if (dense_grid > kPartHalf) dense_grid = kPartHalf;
   if (grad_heads) {
+    YH_TIME(YH_K_LOSS_DENSE, s);
     loss_dense_kernel<true><<<dense_grid, kDenseThreads, 0, s>>>(
         tab, g, B, 0.f, numel, p.w_obj, p.reduction, ws->partials);
   } else {
+    YH_TIME(YH_K_LOSS_DENSE, s);
     loss_dense_kernel<false><<<dense_grid, kDenseThreads, 0, s>>>(
         tab, g, B, 0.f, numel, p.w_obj, p.reduction, ws->partials);
   }
-  YH_LAUNCHED();
+  YH_LAUNCHED(s);
   int row_grid = ws->num_sms * 2;
   const int need = (capacity + (kRowThreads / 32) - 1) / (kRowThreads / 32);
   if (row_grid > need) row_grid = need;
   if (row_grid < 1) row_grid = 1;
   if (row_grid > kPartHalf) row_grid = kPartHalf;
+  YH_TIME(YH_K_LOSS_ROWS, s);
   loss_rows_kernel<<<row_grid, kRowThreads, 0, s>>>(
       tab, g, p, (const long long*)m_batch, (const long long*)m_flat, m_target,
       (const long long*)m_class, M_dev, capacity, iou_score_dev, pred_rows_dev, ws->partials,
       dense_grid, ws->ticket, losses4_dev);
-  YH_LAUNCHED();
+  YH_LAUNCHED(s);
   return YH_OK;
 }

@@ -505,8 +505,9 @@ static int launch_segments(const P& prov, const SegView& v, int S, double iou_th
                                  (int)smem));
     attr_set = true;
   }
+  YH_TIME(YH_K_NMS_SEGMENT, s);
   nms_segment_kernel<P><<<S, kNmsThreads, smem, s>>>(prov, v, iou_thr);
-  YH_LAUNCHED();
+  YH_LAUNCHED(s);
   return YH_OK;
 }
 
@@ -553,15 +554,17 @@ int yh_nms(YhWorkspace* ws, const float* const* heads, const YhLayer* layers, in
   YH_CUDA(cudaMemsetAsync(ws->cand_count, 0, (size_t)B * sizeof(int), s));
   SegView v = make_view(ws);
   dim3 grid((prov.t.N + kFilterThreads - 1) / kFilterThreads, B);
+  YH_TIME(YH_K_NMS_FILTER, s);
   nms_filter_kernel<<<grid, kFilterThreads, 0, s>>>(prov.t, (float)confidence_threshold, v.keys,
                                                     (int)v.stride, v.cap, v.count, ws->err_flag);
-  YH_LAUNCHED();
+  YH_LAUNCHED(s);
   rc = launch_segments(prov, v, B, iou_threshold, s);
   if (rc) return rc;
+  YH_TIME(YH_K_NMS_EMIT, s);
   nms_emit_kernel<<<B, 256, 0, s>>>(v, B, prov.t.N, (long long*)kb, (long long*)kc,
                                     (long long*)ki, tlbr, conf, nullptr, out_K_dev, capacity,
                                     ws->err_flag);
-  YH_LAUNCHED();
+  YH_LAUNCHED(s);
   return YH_OK;
 }
 
@@ -585,16 +588,18 @@ int yh_nms_by_scores(YhWorkspace* ws, const float* ltrb, const float* scores,
   SegView v = make_view(ws);
   v.stride = room;  // one segment over the whole region
   v.cap = K;
+  YH_TIME(YH_K_NMS_PACK, s);
   nms_pack_kernel<<<(K + 255) / 256, 256, 0, s>>>(scores, K, v.keys, v.count);
-  YH_LAUNCHED();
+  YH_LAUNCHED(s);
   ArrayBoxes prov;
   prov.ltrb = ltrb;
   prov.groups = (const long long*)groups;
   int rc = launch_segments(prov, v, 1, iou_threshold, s);
   if (rc) return rc;
+  YH_TIME(YH_K_NMS_EMIT, s);
   nms_emit_kernel<<<1, 256, 0, s>>>(v, 1, 1, nullptr, nullptr, nullptr, nullptr, nullptr,
                                     (long long*)keep, out_K_dev, K, ws->err_flag);
-  YH_LAUNCHED();
+  YH_LAUNCHED(s);
   return YH_OK;
 }
 
@@ -607,10 +612,11 @@ int yh_inference_pick(YhWorkspace* ws, int64_t* kb, int64_t* kc, int64_t* ki, fl
   YH_REQUIRE(capacity >= 0, "capacity=%d", capacity);
   cudaStream_t s = (cudaStream_t)stream;
   YH_CUDA(cudaSetDevice(ws->device));
+  YH_TIME(YH_K_PICK, s);
   pick_kernel<<<1, kNmsThreads, 0, s>>>((long long*)kb, (long long*)kc, (long long*)ki, tlbr, conf,
                                         io_K_dev, capacity, ws->slot_dist, ws->max_batch,
                                         (long long)ws->max_instances);
-  YH_LAUNCHED();
+  YH_LAUNCHED(s);
   return YH_OK;
 }
 
