@@ -1,0 +1,156 @@
+"""Whole hot-path step (decode -> assign -> loss fwd+bwd -> NMS) on preallocated buffers.
+
+`DeviceStep` is what a training worker does per batch after the backbone
+(train/src/train/single_gpu.rs:152-186) with every buffer allocated once: four C-ABI calls, no
+host synchronisation.  `HostStep` is the same step for callers whose tensors live in HOST memory
+(the end-to-end form measured by bench.py): pinned staging, H2D of the head tensors and labels,
+the step, D2H of losses / matches / detections and of the head gradients.
+"""
+import ctypes
+from typing import List, Optional, Sequence
+
+import torch
+
+from . import _lib
+from .loss import YoloLossInit, pack_labels
+from .tensors import DetectionInfo
+from .detect import MergedDenseDetection
+from .workspace import Workspace
+
+
+class DeviceStep:
+    def __init__(self, spec, batch: int, device: torch.device, loss: YoloLossInit = None,
+                 nms_conf=0.4, nms_iou=0.5, by_class=True, max_gt=None, cand_per_image=8192,
+                 max_detections=None, with_grad=True):
+        self.lib = _lib.load()
+        self.spec, self.B, self.dev = spec, batch, device
+        self.C = spec.num_classes
+        self.info: List[DetectionInfo] = MergedDenseDetection.make_info(spec.shapes, spec.anchors)
+        self.layers = _lib.make_layers(self.info)
+        self.L = len(self.info)
+        self.N = sum(i.size for i in self.info)
+        init = loss or YoloLossInit(box_metric="ciou")
+        self.yolo_loss = init.build()  # validated config
+        self.cfg = self.yolo_loss._cfg
+        self.rect4 = 1 if init.match_grid_method == "Rect4" else 0
+        self.thresh = float(init.anchor_scale_thresh)
+        self.nms_conf, self.nms_iou, self.by_class = float(nms_conf), float(nms_iou), 1 if by_class else 0
+        self.ws = Workspace()
+        self.ws.ensure(device, batch, self.N, cand_per_image)
+        f32, i64, i32 = torch.float32, torch.int64, torch.int32
+        self.boxes = torch.empty((4, batch, 1, self.N), dtype=f32, device=device)
+        max_gt = max_gt or 32 * batch
+        self.mcap = max_gt * sum(i.A for i in self.info) * (5 if self.rect4 else 3)
+        self.m_batch = torch.empty(self.mcap, dtype=i64, device=device)
+        self.m_flat = torch.empty(self.mcap, dtype=i64, device=device)
+        self.m_gt = torch.empty(self.mcap, dtype=i32, device=device)
+        self.m_target = torch.empty((self.mcap, 4), dtype=f32, device=device)
+        self.m_class = torch.empty(self.mcap, dtype=i64, device=device)
+        self.M = torch.zeros(1, dtype=i32, device=device)
+        self.losses4 = torch.zeros(4, dtype=f32, device=device)
+        self.iou_score = torch.empty(self.mcap, dtype=f32, device=device)
+        self.pred_rows = torch.empty((self.mcap, self.C + 5), dtype=f32, device=device)
+        self.grads = [torch.empty(spec.head_shape(l, batch), dtype=f32, device=device)
+                      for l in range(self.L)] if with_grad else None
+        self.kcap = max_detections or batch * 1024
+        self.kb = torch.empty(self.kcap, dtype=i64, device=device)
+        self.kc = torch.empty(self.kcap, dtype=i64, device=device)
+        self.ki = torch.empty(self.kcap, dtype=i64, device=device)
+        self.tlbr = torch.empty((self.kcap, 4), dtype=f32, device=device)
+        self.conf = torch.empty(self.kcap, dtype=f32, device=device)
+        self.K = torch.zeros(1, dtype=i32, device=device)
+        self._grad_ptrs = _lib.ptr_array(self.grads) if with_grad else None
+
+    def algorithmic_bytes(self):
+        """SURVEY.md §8d per-image figures x batch, per kernel (M-dependent part excluded)."""
+        n = self.N * self.B
+        return {"decode_kernel": 32 * n, "loss_dense_kernel": 344 * n, "nms_filter_kernel": 340 * n}
+
+    def run(self, heads: Sequence[torch.Tensor], gt_dev: torch.Tensor, off_dev: torch.Tensor, stream=None):
+        """heads: L contiguous f32 CUDA tensors [B, A*(5+C), H, W]; gt_dev [G,5] f64; off_dev [B+1] i32.
+        Enqueues 8 kernels on the current stream; nothing synchronises."""
+        s = stream if stream is not None else torch.cuda.current_stream(self.dev).cuda_stream
+        lib, ck = self.lib, _lib.check
+        hp = _lib.ptr_array(heads)
+        b = self.boxes
+        ck(lib.yh_decode_merged(hp, self.layers, self.L, self.B, self.C, b[0].data_ptr(), b[1].data_ptr(),
+                                b[2].data_ptr(), b[3].data_ptr(), self.N, s))
+        ck(lib.yh_assign(self.ws.handle, gt_dev.data_ptr(), off_dev.data_ptr(), self.B, self.layers, self.L,
+                         self.rect4, self.thresh, self.m_batch.data_ptr(), self.m_flat.data_ptr(),
+                         self.m_gt.data_ptr(), self.m_target.data_ptr(), self.m_class.data_ptr(),
+                         self.M.data_ptr(), self.mcap, s))
+        ck(lib.yh_loss_fwd_bwd(self.ws.handle, hp, self.layers, self.L, self.B, self.C,
+                               self.m_batch.data_ptr(), self.m_flat.data_ptr(), self.m_target.data_ptr(),
+                               self.m_class.data_ptr(), self.M.data_ptr(), self.mcap, self.cfg,
+                               self.losses4.data_ptr(), self.iou_score.data_ptr(), self.pred_rows.data_ptr(),
+                               self._grad_ptrs, s))
+        ck(lib.yh_nms(self.ws.handle, hp, self.layers, self.L, self.B, self.C, self.nms_conf, self.nms_iou,
+                      self.by_class, self.kb.data_ptr(), self.kc.data_ptr(), self.ki.data_ptr(),
+                      self.tlbr.data_ptr(), self.conf.data_ptr(), self.K.data_ptr(), self.kcap, s))
+
+    def counts(self):
+        """synchronising read of (M, K); raises on overflow."""
+        return self.ws.read_counts(torch.cuda.current_stream(self.dev).cuda_stream, self.M, self.K)
+
+
+class HostStep:
+    """The step for HOST-resident inputs and outputs.  Per call: H2D of the L head tensors and
+    the packed labels from pinned memory, DeviceStep, D2H of [losses4, M, K], the match list, the
+    kept detections and (if `with_grad`) the L head-gradient tensors into pinned memory."""
+
+    def __init__(self, spec, batch, device, with_grad=True, **kw):
+        self.step = DeviceStep(spec, batch, device, with_grad=with_grad, **kw)
+        st = self.step
+        self.d_heads = [torch.empty(spec.head_shape(l, batch), dtype=torch.float32, device=device)
+                        for l in range(st.L)]
+        pin = dict(pin_memory=True)
+        self.h_losses = torch.empty(4, dtype=torch.float32, **pin)
+        self.h_counts = torch.empty(2, dtype=torch.int32, **pin)
+        self.h_match = torch.empty((2, st.mcap), dtype=torch.int64, **pin)
+        self.h_det = torch.empty((3, st.kcap), dtype=torch.int64, **pin)
+        self.h_tlbr = torch.empty((st.kcap, 4), dtype=torch.float32, **pin)
+        self.h_conf = torch.empty(st.kcap, dtype=torch.float32, **pin)
+        self.h_grads = [torch.empty(spec.head_shape(l, batch), dtype=torch.float32, **pin)
+                        for l in range(st.L)] if with_grad else None
+        self.max_gt = st.mcap // (sum(i.A for i in st.info) * (5 if st.rect4 else 3))
+        self.d_gt = torch.empty((self.max_gt, 5), dtype=torch.float64, device=device)
+        self.d_off = torch.empty(batch + 1, dtype=torch.int32, device=device)
+        self.h2d_bytes = 0
+        self.d2h_bytes = 0
+
+    def run(self, host_heads: Sequence[torch.Tensor], gt_host: torch.Tensor, off_host: torch.Tensor):
+        """host_heads / gt_host / off_host: pinned host tensors.  Returns (losses4, M, K) on the
+        host after one stream synchronisation; detections / matches / gradients are in the
+        pinned h_* buffers."""
+        st = self.step
+        G = gt_host.shape[0]
+        if G > self.max_gt:
+            raise ValueError(f"{G} labels exceed the capacity {self.max_gt}")
+        h2d = 0
+        for d, h in zip(self.d_heads, host_heads):
+            d.copy_(h, non_blocking=True)
+            h2d += h.numel() * 4
+        self.d_gt[:G].copy_(gt_host, non_blocking=True)
+        self.d_off.copy_(off_host, non_blocking=True)
+        h2d += G * 40 + off_host.numel() * 4
+        st.run(self.d_heads, self.d_gt[:G], self.d_off)
+        # results: scalars first (small), then the bulk
+        self.h_losses.copy_(st.losses4, non_blocking=True)
+        self.h_counts[0:1].copy_(st.M, non_blocking=True)
+        self.h_counts[1:2].copy_(st.K, non_blocking=True)
+        self.h_match[0].copy_(st.m_batch, non_blocking=True)
+        self.h_match[1].copy_(st.m_flat, non_blocking=True)
+        self.h_det[0].copy_(st.kb, non_blocking=True)
+        self.h_det[1].copy_(st.kc, non_blocking=True)
+        self.h_det[2].copy_(st.ki, non_blocking=True)
+        self.h_tlbr.copy_(st.tlbr, non_blocking=True)
+        self.h_conf.copy_(st.conf, non_blocking=True)
+        d2h = 16 + 8 + self.h_match.numel() * 8 + self.h_det.numel() * 8 + self.h_tlbr.numel() * 4 \
+            + self.h_conf.numel() * 4
+        if self.h_grads is not None:
+            for h, d in zip(self.h_grads, st.grads):
+                h.copy_(d, non_blocking=True)
+                d2h += d.numel() * 4
+        torch.cuda.current_stream(st.dev).synchronize()
+        self.h2d_bytes, self.d2h_bytes = h2d, d2h
+        return self.h_losses, int(self.h_counts[0]), int(self.h_counts[1])
