@@ -12,7 +12,8 @@ the 126 MB L2, so every step streams from HBM) and 1..30 GT boxes per image; CIo
 reference's default weights, Rect4 matching, NMS at the shipped thresholds (conf .4 / IoU .5,
 train.json5:153-154) per class.  Weak scaling: every rank owns its own 64 images; the only
 collective is the 5-float loss all-reduce.  One step = yh_decode_merged + yh_assign +
-yh_loss_fwd_bwd (with the full head gradient) + yh_nms = 8 kernel launches.
+yh_loss_dense + yh_loss_rows (with the full head gradient) + yh_nms = 8 kernels, captured once as
+a CUDA graph over four forked/joined streams (yolo_dl_b200/pipeline.py) and replayed per step.
 """
 import argparse
 import json
@@ -34,8 +35,8 @@ NMS_CONF, NMS_IOU, BY_CLASS = 0.4, 0.5, True
 def parse():
     p = argparse.ArgumentParser()
     p.add_argument("--gpus", type=int, default=1)
-    p.add_argument("--steps", type=int, default=50)
-    p.add_argument("--warmup", type=int, default=5)
+    p.add_argument("--steps", type=int, default=1000)
+    p.add_argument("--warmup", type=int, default=10)
     p.add_argument("--impl", default="native", choices=["native", "reference"])
     p.add_argument("--batch", type=int, default=64, help="images per GPU")
     p.add_argument("--cpu-sample", type=int, default=8, help="images per CPU-baseline sample")
@@ -85,7 +86,7 @@ class ClockSampler:
                         self.reasons.add(name)
             except Exception:
                 pass
-            self._stop.wait(0.02)
+            self._stop.wait(0.002)
 
     def __enter__(self):
         if self.nv:
@@ -197,8 +198,11 @@ def run_native(args):
     gt_d, off_d = gt_h.to(dev), off_h.to(dev)
     step = DeviceStep(spec, B, dev, nms_conf=NMS_CONF, nms_iou=NMS_IOU, by_class=BY_CLASS)
 
+    # the step as a CUDA graph: 8 kernels on 4 forked/joined streams (pipeline.run_overlapped)
+    step.capture(heads, gt_d, off_d)
+
     def one_step():
-        step.run(heads, gt_d, off_d)
+        step.replay()
         if world > 1:  # the loss-scalar exchange data-parallel training needs
             ydist.weighted_mean_losses(step.losses4, B)
 
@@ -206,7 +210,6 @@ def run_native(args):
         one_step()
     M, Kdet = step.counts()
     barrier()
-    lib.yh_launch_count(1)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(local) as clk:
         barrier()
@@ -215,13 +218,26 @@ def run_native(args):
             one_step()
         e1.record()
         barrier()
-    launches = int(lib.yh_launch_count(1))
+    launches = step.kernels_in_graph * K
     ms = e0.elapsed_time(e1)
     if world > 1:
         t = torch.tensor([ms], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t)
     value = world * B * K / (ms * 1e-3)
+
+    # the same 8 kernels launched one after another on one stream (no graph), for comparison
+    Ks = max(3, min(K, 50))
+    for _ in range(3):
+        step.run(heads, gt_d, off_d)
+    barrier()
+    q0, q1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    q0.record()
+    for _ in range(Ks):
+        step.run(heads, gt_d, off_d)
+    q1.record()
+    barrier()
+    seq_ms = q0.elapsed_time(q1) / Ks
 
     # per-kernel device times, measured live with CUDA events on the launch stream
     import ctypes
@@ -295,6 +311,8 @@ def run_native(args):
                 "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f32", "data": "synthetic", "config": workload_config(args, world),
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches,
+                "execution": "CUDA graph of 8 kernels on 4 forked/joined streams, replayed once per step",
+                "sequential_ms_per_step": seq_ms,
                 "clocks": clk.summary(), "matches_per_step": M, "detections_per_step": Kdet,
                 "loss": float(step.losses4[0])}
         print(json.dumps(line), flush=True)

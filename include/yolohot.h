@@ -148,6 +148,24 @@ int yh_loss_fwd_bwd(YhWorkspace* ws, const float* const* heads, const YhLayer* l
                     float* iou_score_dev, float* pred_rows_dev, float* const* grad_heads,
                     void* stream);
 
+/* The two phases of yh_loss_fwd_bwd as separate calls, so that a caller with streams can overlap
+ * them with the rest of the step (YoloLoss::forward does assign -> loss strictly in sequence,
+ * `loss_.rs:233-256`, although the dense objectness pass needs no matches):
+ *   yh_loss_dense  the objectness BCE over all B*N cells against target 0 and, if grad_heads, the
+ *                  whole head gradient (zeros + sigmoid(x)*w/(B*N)).  Needs only the heads: may
+ *                  run concurrently with yh_assign / yh_decode / yh_nms on other streams.
+ *   yh_loss_rows   the M matched rows (box metric, class BCE, objectness correction, their
+ *                  gradients) and the final reduction into losses4_dev.  Must be ordered after
+ *                  yh_loss_dense on the same workspace and after yh_assign.
+ * yh_loss_fwd_bwd == yh_loss_dense; yh_loss_rows on one stream. */
+int yh_loss_dense(YhWorkspace* ws, const float* const* heads, const YhLayer* layers, int L, int B,
+                  int C, const YhLossCfg* cfg, float* const* grad_heads, void* stream);
+int yh_loss_rows(YhWorkspace* ws, const float* const* heads, const YhLayer* layers, int L, int B,
+                 int C, const int64_t* m_batch, const int64_t* m_flat, const float* m_target,
+                 const int64_t* m_class, const int32_t* M_dev, int capacity, const YhLossCfg* cfg,
+                 float* losses4_dev, float* iou_score_dev, float* pred_rows_dev,
+                 float* const* grad_heads, void* stream);
+
 /* ---- a12+a13: NonMaxSuppression::forward (`yolo-dl/src/loss/nms.rs:72-170`) incl. the
  * grouped greedy NMS of tch_nms::nms_by_scores (call site nms.rs:142-148).
  * conf = sigmoid(obj)*sigmoid(cls); candidates: sigmoid(obj) >= thr && conf >= thr (f32

@@ -1,0 +1,132 @@
+"""DeviceStep / HostStep: the whole step on preallocated buffers.  The sequential form, the
+fork/join form over four streams and its CUDA-graph replay must give bit-identical results
+(every reduction is fixed-order), and all of them must agree with the oracle."""
+import numpy as np
+import pytest
+import torch
+
+import yolo_dl_b200 as yh
+from oracle import detect as odet, loss as oloss, nms as onms
+from yolo_dl_b200 import synth
+from yolo_dl_b200.pipeline import DeviceStep, HostStep
+from util import close, grad_close
+
+pytestmark = pytest.mark.gpu
+
+
+def snapshot(step):
+    torch.cuda.synchronize()
+    M, K = step.counts()
+    return {
+        "M": M, "K": K,
+        "losses": step.losses4.clone(),
+        "boxes": step.boxes.clone(),
+        "m_batch": step.m_batch[:M].clone(), "m_flat": step.m_flat[:M].clone(),
+        "m_gt": step.m_gt[:M].clone(), "iou": step.iou_score[:M].clone(),
+        "kb": step.kb[:K].clone(), "kc": step.kc[:K].clone(), "ki": step.ki[:K].clone(),
+        "tlbr": step.tlbr[:K].clone(), "conf": step.conf[:K].clone(),
+        "grads": [g.clone() for g in step.grads],
+    }
+
+
+def same(a, b):
+    assert a["M"] == b["M"] and a["K"] == b["K"]
+    for k in a:
+        if k in ("M", "K"):
+            continue
+        xs, ys = (a[k], b[k]) if isinstance(a[k], list) else ([a[k]], [b[k]])
+        for x, y in zip(xs, ys):
+            assert torch.equal(x, y), k
+
+
+@pytest.mark.parametrize("name,B", [("small", 3), ("yolov4_608", 4), ("yolov4_tiny_416", 16)])
+def test_overlapped_and_graph_equal_sequential_and_oracle(dev, name, B):
+    spec = synth.small_spec() if name == "small" else getattr(synth, name)()
+    om_, cm_ = (-2.0, -1.0) if name == "small" else (-3.5, -2.5)
+    heads_cpu = synth.make_heads(spec, B, synth.SEED0 + 5, obj_mean=om_, cls_mean=cm_)
+    targets = synth.make_targets(spec, B, synth.SEED0 + 5, n_max=12)
+    heads = [h.to(dev) for h in heads_cpu]
+    gt_h, off_h = yh.pack_labels(targets)
+    gt, off = gt_h.to(dev), off_h.to(dev)
+    step = DeviceStep(spec, B, dev, nms_conf=0.3, nms_iou=0.5, by_class=True, cand_per_image=16384,
+                      max_detections=B * 16384)
+
+    step.run(heads, gt, off)
+    seq = snapshot(step)
+
+    for g in step.grads:
+        g.fill_(float("nan"))
+    step.losses4.fill_(float("nan"))
+    step.run_overlapped(heads, gt, off)
+    same(seq, snapshot(step))
+
+    step.capture(heads, gt, off)
+    assert step.kernels_in_graph == DeviceStep.KERNELS_PER_STEP
+    for _ in range(3):
+        for g in step.grads:
+            g.fill_(float("nan"))
+        step.losses4.fill_(float("nan"))
+        step.boxes.fill_(float("nan"))
+        step.replay()
+        same(seq, snapshot(step))
+
+    # and against the oracle
+    infos = odet.make_infos(spec.shapes, spec.anchors)
+    ref = oloss.yolo_loss(heads_cpu, infos, spec.num_classes, targets, oloss.LossConfig(box_metric="ciou"))
+    close(seq["losses"][0], ref["losses"]["total"], what="total")
+    assert np.array_equal(seq["m_flat"].cpu().numpy(), ref["matches"][1])
+    for g, r in zip(seq["grads"], ref["grads"]):
+        grad_close(g, r, what="grad")
+    om = odet.forward_merged(heads_cpu, infos, spec.num_classes)
+    close(seq["boxes"][0], om["cy"], what="cy")
+    ok = onms.nms_forward(om, 0.3, 0.5, True)
+    assert np.array_equal(seq["ki"].cpu().numpy(), ok["instances"])
+    assert np.array_equal(seq["kc"].cpu().numpy(), ok["classes"])
+
+
+def test_graph_replay_follows_refilled_inputs(dev):
+    spec = synth.small_spec()
+    B = 4
+    step = DeviceStep(spec, B, dev, nms_conf=0.3)
+    heads = [h.to(dev) for h in synth.make_heads(spec, B, 1, obj_mean=-1.0, cls_mean=-1.0)]
+    t1 = synth.make_targets(spec, B, 1, n_max=5)
+    gt_h, off_h = yh.pack_labels(t1)
+    G = 64
+    gt = torch.zeros((G, 5), dtype=torch.float64, device=dev)
+    off = off_h.to(dev)
+    gt[:gt_h.shape[0]] = gt_h.to(dev)
+    step.capture(heads, gt, off)
+    # new batch, same buffers
+    heads2 = synth.make_heads(spec, B, 2, obj_mean=-1.0, cls_mean=-1.0)
+    t2 = synth.make_targets(spec, B, 2, n_max=5)
+    gt2, off2 = yh.pack_labels(t2)
+    for d, h in zip(heads, heads2):
+        d.copy_(h)
+    gt[:gt2.shape[0]] = gt2.to(dev)
+    off.copy_(off2)
+    step.replay()
+    got = snapshot(step)
+    infos = odet.make_infos(spec.shapes, spec.anchors)
+    ref = oloss.yolo_loss(heads2, infos, spec.num_classes, t2, oloss.LossConfig(box_metric="ciou"))
+    close(got["losses"][0], ref["losses"]["total"], what="total")
+    assert np.array_equal(got["m_flat"].cpu().numpy(), ref["matches"][1])
+
+
+def test_host_step_round_trip(dev):
+    spec = synth.small_spec()
+    B = 5
+    heads_cpu = synth.make_heads(spec, B, 9, obj_mean=-1.0, cls_mean=-1.0)
+    targets = synth.make_targets(spec, B, 9, n_max=6)
+    gt_h, off_h = yh.pack_labels(targets)
+    hs = HostStep(spec, B, dev, nms_conf=0.3)
+    pinned = [h.pin_memory() for h in heads_cpu]
+    for _ in range(2):
+        losses, M, K = hs.run(pinned, gt_h.pin_memory(), off_h.pin_memory())
+    infos = odet.make_infos(spec.shapes, spec.anchors)
+    ref = oloss.yolo_loss(heads_cpu, infos, spec.num_classes, targets, oloss.LossConfig(box_metric="ciou"))
+    close(losses[0], ref["losses"]["total"], what="total")
+    assert M == len(ref["matches"][1])
+    assert np.array_equal(hs.h_match[1][:M].numpy(), ref["matches"][1])
+    for g, r in zip(hs.h_grads, ref["grads"]):
+        grad_close(g, r, what="grad")
+    assert hs.h2d_bytes > 0 and hs.d2h_bytes > 0

@@ -56,6 +56,11 @@ SYMBOLS = {
     "yh_loss_fwd_bwd": (c_int, [c_void_p, _PF, POINTER(YhLayer), c_int, c_int, c_int, c_void_p,
                                 c_void_p, c_void_p, c_void_p, c_void_p, c_int, POINTER(YhLossCfg),
                                 c_void_p, c_void_p, c_void_p, _PF, c_void_p]),
+    "yh_loss_dense": (c_int, [c_void_p, _PF, POINTER(YhLayer), c_int, c_int, c_int, POINTER(YhLossCfg),
+                              _PF, c_void_p]),
+    "yh_loss_rows": (c_int, [c_void_p, _PF, POINTER(YhLayer), c_int, c_int, c_int, c_void_p,
+                             c_void_p, c_void_p, c_void_p, c_void_p, c_int, POINTER(YhLossCfg),
+                             c_void_p, c_void_p, c_void_p, _PF, c_void_p]),
     "yh_nms": (c_int, [c_void_p, _PF, POINTER(YhLayer), c_int, c_int, c_int, c_double, c_double,
                        c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
                        c_void_p]),

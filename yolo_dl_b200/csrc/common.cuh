@@ -171,4 +171,4 @@ struct YhWorkspace {
   int32_t* host_counts;           // pinned, [max_batch + 8]
 };
 
-#define YH_PARTIALS_MAX 4096
+#define YH_PARTIALS_MAX 8192

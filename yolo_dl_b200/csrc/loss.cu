@@ -54,59 +54,86 @@ __device__ __forceinline__ float softplus_f(float x) {
 // ---------------------------------------------------------------------------------
 // K4
 // ---------------------------------------------------------------------------------
+// GRAD: the flat gradient tensor of every layer is cut into tiles of kTileQuads float4 quads
+// (32 KB); a tile never straddles two layers.  One 64-bit modulo per TILE (not per store)
+// tells whether the tile intersects an objectness plane (floats [4*run, 5*run) of an image):
+//   * it does not (~97 % of the tiles): kTileUnroll unconditional 16-byte streaming zero
+//     stores per thread — no loads, no address arithmetic beyond an immediate offset.
+//     tools/fill_bench.cu measured this form at 6.0-6.3 TB/s on B200 (cudaMemset: 6.6-6.8),
+//     level with TMA bulk stores from a zeroed shared buffer, so the simpler form is used;
+//   * it does: per-quad classification with a single conditional wrap instead of a modulo.
+constexpr int kTileUnroll = 8;
+constexpr int kTileQuads = kDenseThreads * kTileUnroll;  // 2048 quads = 8192 floats = 32 KB
+constexpr int kTileFloats = kTileQuads * 4;
+
 template <bool GRAD>
 __global__ void __launch_bounds__(kDenseThreads)
-loss_dense_kernel(const LayerTab t, const GradTab g, const int B, const float inv_numel_scale_w,
-                  const float numel, const float w_obj, const int reduction,
-                  double* __restrict__ partials) {
-  // work space: per layer, float4 quads (GRAD) or obj elements (!GRAD)
-  long long prefix[YH_MAX_LAYERS + 1];
-  prefix[0] = 0;
-#pragma unroll
-  for (int l = 0; l < YH_MAX_LAYERS; ++l) {
-    long long n = 0;
-    if (l < t.L) {
-      n = GRAD ? ((long long)B * t.A[l] * t.E * t.HW[l] + 3) / 4
-               : (long long)B * t.A[l] * t.HW[l];
-    }
-    prefix[l + 1] = prefix[l] + n;
-  }
-  const long long total = prefix[YH_MAX_LAYERS];
-  const long long stride = (long long)gridDim.x * kDenseThreads;
+loss_dense_kernel(const LayerTab t, const GradTab g, const int B, const float numel,
+                  const float w_obj, const int reduction, double* __restrict__ partials) {
   double acc = 0.0;
-  (void)inv_numel_scale_w;
-
-  for (long long i = (long long)blockIdx.x * kDenseThreads + threadIdx.x; i < total; i += stride) {
-    int l = 0;
+  if (GRAD) {
+    long long prefix[YH_MAX_LAYERS + 1];  // in tiles
+    prefix[0] = 0;
 #pragma unroll
-    for (int k = 1; k < YH_MAX_LAYERS; ++k)
-      if (k < t.L && i >= prefix[k]) l = k;
-    const long long li = i - prefix[l];
-    const int run = t.A[l] * t.HW[l];                 // floats per entry per image
-    const long long per_img = (long long)run * t.E;   // floats per image
-    const float* __restrict__ head = t.head[l];
-    if (GRAD) {
+    for (int l = 0; l < YH_MAX_LAYERS; ++l) {
+      long long n = 0;
+      if (l < t.L) {
+        const long long quads = ((long long)B * t.A[l] * t.E * t.HW[l] + 3) / 4;
+        n = (quads + kTileQuads - 1) / kTileQuads;
+      }
+      prefix[l + 1] = prefix[l] + n;
+    }
+    const long long total = prefix[YH_MAX_LAYERS];
+    const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (long long tile = blockIdx.x; tile < total; tile += gridDim.x) {
+      int l = 0;
+#pragma unroll
+      for (int k = 1; k < YH_MAX_LAYERS; ++k)
+        if (k < t.L && tile >= prefix[k]) l = k;
+      const long long run = (long long)t.A[l] * t.HW[l];  // floats per entry per image
+      const long long per_img = run * t.E;                // floats per image
       const long long len = (long long)B * per_img;
-      const long long idx = li * 4;
-      // offset inside the image; 32-bit modulo whenever the layer tensor allows it
-      const long long r = (len < (1LL << 32))
-                              ? (long long)((unsigned)idx % (unsigned)per_img)
-                              : idx % per_img;
-      float* gp = g.grad[l] + idx;
-      const bool full = idx + 3 < len;
-      // obj channels of an image: [4*run, 5*run)
-      const bool touches = (r + 3 >= 4LL * run) && (r < 5LL * run);
-      if (full && !touches) {
-        st_stream4(reinterpret_cast<float4*>(gp), make_float4(0.f, 0.f, 0.f, 0.f));
-      } else {
+      const long long idx0 = (tile - prefix[l]) * kTileFloats;  // first float of the tile
+      const long long r0 = idx0 % per_img;                      // its offset inside the image
+      const long long o0 = 4 * run, o1 = 5 * run;               // obj plane of an image
+      float* __restrict__ gbase = g.grad[l] + idx0;
+      const bool whole = idx0 + kTileFloats <= len;
+      const bool one_wrap = per_img >= kTileFloats + 4;
+      const bool touches = !one_wrap || (r0 + kTileFloats > o0 && r0 < o1) ||
+                           (r0 + kTileFloats > per_img + o0);
+      if (whole && !touches) {
+        float4* q = reinterpret_cast<float4*>(gbase) + threadIdx.x;
+#pragma unroll
+        for (int u = 0; u < kTileUnroll; ++u) st_stream4(q + u * kDenseThreads, zero4);
+        continue;
+      }
+      const float* __restrict__ hbase = t.head[l] + idx0;
+#pragma unroll 2
+      for (int u = 0; u < kTileUnroll; ++u) {
+        const int qi = u * kDenseThreads + threadIdx.x;
+        const long long idx = idx0 + 4LL * qi;
+        if (idx >= len) break;
+        long long r = r0 + 4LL * qi;
+        if (one_wrap) {
+          if (r >= per_img) r -= per_img;
+        } else {
+          r %= per_img;
+        }
+        const bool full = idx + 3 < len;
+        const bool hit = (r + 3 >= o0 && r < o1) || (r + 3 >= per_img + o0);
+        float* gp = gbase + 4 * qi;
+        if (full && !hit) {
+          st_stream4(reinterpret_cast<float4*>(gp), zero4);
+          continue;
+        }
         float v[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
           if (idx + k < len) {
             long long rk = r + k;
             if (rk >= per_img) rk -= per_img;
-            if (rk >= 4LL * run && rk < 5LL * run) {
-              const float x = __ldcs(head + idx + k);
+            if (rk >= o0 && rk < o1) {
+              const float x = __ldcs(hbase + 4 * qi + k);
               acc += (double)softplus_f(x);
               // BCE backward, target 0: sigmoid(x) [/numel for Mean] * upstream w_obj
               float gi = sigmoid_f(x);
@@ -123,10 +150,27 @@ loss_dense_kernel(const LayerTab t, const GradTab g, const int B, const float in
             if (idx + k < len) st_stream1(gp + k, v[k]);
         }
       }
-    } else {
+    }
+  } else {
+    // forward only: just the objectness planes
+    long long prefix[YH_MAX_LAYERS + 1];
+    prefix[0] = 0;
+#pragma unroll
+    for (int l = 0; l < YH_MAX_LAYERS; ++l)
+      prefix[l + 1] = prefix[l] + ((l < t.L) ? (long long)B * t.A[l] * t.HW[l] : 0LL);
+    const long long total = prefix[YH_MAX_LAYERS];
+    const long long stride = (long long)gridDim.x * kDenseThreads;
+    for (long long i = (long long)blockIdx.x * kDenseThreads + threadIdx.x; i < total; i += stride) {
+      int l = 0;
+#pragma unroll
+      for (int k = 1; k < YH_MAX_LAYERS; ++k)
+        if (k < t.L && i >= prefix[k]) l = k;
+      const long long li = i - prefix[l];
+      const int run = t.A[l] * t.HW[l];
+      const long long per_img = (long long)run * t.E;
       const long long b = li / run;
       const long long j = li - b * run;
-      const float x = __ldcs(head + b * per_img + 4LL * run + j);
+      const float x = __ldcs(t.head[l] + b * per_img + 4LL * run + j);
       acc += (double)softplus_f(x);
     }
   }
@@ -297,8 +341,18 @@ loss_rows_kernel(const LayerTab t, const GradTab g, const LossParams p,
     const float* hp = t.head[l] + off;
     float* gp = want_grad ? g.grad[l] + off : nullptr;
 
-    // the five leading logits (same address across the warp: one broadcast transaction each)
-    const float x0 = hp[0], x1 = hp[es], x2 = hp[2 * es], x3 = hp[3 * es], xo = hp[4 * es];
+    // every load of the row is issued before anything is consumed: lanes 0..4 fetch the five
+    // leading logits (then broadcast by shuffle), every lane its first three class logits
+    const float xl = (lane < 5) ? hp[(size_t)lane * es] : 0.0f;
+    float xc[3];
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      const int k = lane + 32 * j;
+      xc[j] = (k < t.C) ? hp[(size_t)(5 + k) * es] : 0.0f;
+    }
+    const float x0 = __shfl_sync(0xffffffffu, xl, 0), x1 = __shfl_sync(0xffffffffu, xl, 1);
+    const float x2 = __shfl_sync(0xffffffffu, xl, 2), x3 = __shfl_sync(0xffffffffu, xl, 3);
+    const float xo = __shfl_sync(0xffffffffu, xl, 4);
     const float s0 = sigmoid_f(x0), s1 = sigmoid_f(x1), s2 = sigmoid_f(x2), s3 = sigmoid_f(x3);
     Box4 pb;
     pb.cy = decode_center(s0, c.row, (float)t.H[l]);
@@ -321,8 +375,8 @@ loss_rows_kernel(const LayerTab t, const GradTab g, const LossParams p,
     // class BCE over C channels, lanes strided
     const int cls = (int)m_class[m];
     float bce = 0.f;
-    for (int k = lane; k < t.C; k += 32) {
-      const float x = hp[(size_t)(5 + k) * es];
+    for (int k = lane, j = 0; k < t.C; k += 32, ++j) {
+      const float x = (j < 3) ? xc[j < 3 ? j : 0] : hp[(size_t)(5 + k) * es];
       const float tt = (k == cls) ? p.cls_pos : p.cls_neg;
       bce += (1.0f - tt) * x + softplus_f(-x);
       if (want_grad) {
@@ -445,16 +499,26 @@ loss_rows_kernel(const LayerTab t, const GradTab g, const LossParams p,
 
 }  // namespace yh
 
-extern "C" int yh_loss_fwd_bwd(YhWorkspace* ws, const float* const* heads, const YhLayer* layers,
-                               int L, int B, int C, const int64_t* m_batch, const int64_t* m_flat,
-                               const float* m_target, const int64_t* m_class,
-                               const int32_t* M_dev, int capacity, const YhLossCfg* cfg,
-                               float* losses4_dev, float* iou_score_dev, float* pred_rows_dev,
-                               float* const* grad_heads, void* stream) {
-  using namespace yh;
+namespace yh {
+
+enum { kPhaseDense = 1, kPhaseRows = 2 };
+
+// Both phases of YoloLoss::forward+backward.  kPhaseDense needs only the heads (it can run
+// concurrently with yh_assign on another stream); kPhaseRows must be ordered after BOTH the
+// dense phase of the same workspace (it overwrites the objectness gradient of the matched
+// cells and folds the dense partial sums into the losses) and yh_assign.
+static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
+                       const YhLayer* layers, int L, int B, int C, const int64_t* m_batch,
+                       const int64_t* m_flat, const float* m_target, const int64_t* m_class,
+                       const int32_t* M_dev, int capacity, const YhLossCfg* cfg,
+                       float* losses4_dev, float* iou_score_dev, float* pred_rows_dev,
+                       float* const* grad_heads, void* stream) {
   YH_REQUIRE(ws != nullptr, "workspace is NULL");
-  YH_REQUIRE(cfg != nullptr && losses4_dev != nullptr && M_dev != nullptr, "NULL argument");
-  YH_REQUIRE(capacity == 0 || (m_batch && m_flat && m_target && m_class), "match list is NULL");
+  YH_REQUIRE(cfg != nullptr, "NULL argument");
+  if (phases & kPhaseRows) {
+    YH_REQUIRE(losses4_dev != nullptr && M_dev != nullptr, "NULL argument");
+    YH_REQUIRE(capacity == 0 || (m_batch && m_flat && m_target && m_class), "match list is NULL");
+  }
   YH_REQUIRE(B >= 1 && B <= ws->max_batch, "B=%d outside 1..max_batch=%d", B, ws->max_batch);
   LayerTab tab;
   int rc = build_layer_tab(layers, L, C, heads, &tab);
@@ -504,19 +568,21 @@ extern "C" int yh_loss_fwd_bwd(YhWorkspace* ws, const float* const* heads, const
   cudaStream_t s = (cudaStream_t)stream;
   YH_CUDA(cudaSetDevice(ws->device));
   const float numel = (float)((long long)B * tab.N);
-  int dense_grid = ws->num_sms * 8;
+  int dense_grid = ws->num_sms * 16;
   if (dense_grid > kPartHalf) dense_grid = kPartHalf;
-  if (grad_heads) {
+  if (!(phases & kPhaseDense)) {
+  } else if (grad_heads) {
     YH_TIME(YH_K_LOSS_DENSE, s);
     loss_dense_kernel<true><<<dense_grid, kDenseThreads, 0, s>>>(
-        tab, g, B, 0.f, numel, p.w_obj, p.reduction, ws->partials);
+        tab, g, B, numel, p.w_obj, p.reduction, ws->partials);
   } else {
     YH_TIME(YH_K_LOSS_DENSE, s);
     loss_dense_kernel<false><<<dense_grid, kDenseThreads, 0, s>>>(
-        tab, g, B, 0.f, numel, p.w_obj, p.reduction, ws->partials);
+        tab, g, B, numel, p.w_obj, p.reduction, ws->partials);
   }
-  YH_LAUNCHED(s);
-  int row_grid = ws->num_sms * 2;
+  if (phases & kPhaseDense) YH_LAUNCHED(s);
+  if (!(phases & kPhaseRows)) return YH_OK;
+  int row_grid = kPartHalf;  // one warp per matched row where the partial slots allow
   const int need = (capacity + (kRowThreads / 32) - 1) / (kRowThreads / 32);
   if (row_grid > need) row_grid = need;
   if (row_grid < 1) row_grid = 1;
@@ -529,3 +595,35 @@ extern "C" int yh_loss_fwd_bwd(YhWorkspace* ws, const float* const* heads, const
   YH_LAUNCHED(s);
   return YH_OK;
 }
+
+}  // namespace yh
+
+extern "C" {
+
+int yh_loss_fwd_bwd(YhWorkspace* ws, const float* const* heads, const YhLayer* layers, int L,
+                    int B, int C, const int64_t* m_batch, const int64_t* m_flat,
+                    const float* m_target, const int64_t* m_class, const int32_t* M_dev,
+                    int capacity, const YhLossCfg* cfg, float* losses4_dev, float* iou_score_dev,
+                    float* pred_rows_dev, float* const* grad_heads, void* stream) {
+  return yh::loss_phases(yh::kPhaseDense | yh::kPhaseRows, ws, heads, layers, L, B, C, m_batch,
+                         m_flat, m_target, m_class, M_dev, capacity, cfg, losses4_dev,
+                         iou_score_dev, pred_rows_dev, grad_heads, stream);
+}
+
+int yh_loss_dense(YhWorkspace* ws, const float* const* heads, const YhLayer* layers, int L, int B,
+                  int C, const YhLossCfg* cfg, float* const* grad_heads, void* stream) {
+  return yh::loss_phases(yh::kPhaseDense, ws, heads, layers, L, B, C, nullptr, nullptr, nullptr,
+                         nullptr, nullptr, 0, cfg, nullptr, nullptr, nullptr, grad_heads, stream);
+}
+
+int yh_loss_rows(YhWorkspace* ws, const float* const* heads, const YhLayer* layers, int L, int B,
+                 int C, const int64_t* m_batch, const int64_t* m_flat, const float* m_target,
+                 const int64_t* m_class, const int32_t* M_dev, int capacity, const YhLossCfg* cfg,
+                 float* losses4_dev, float* iou_score_dev, float* pred_rows_dev,
+                 float* const* grad_heads, void* stream) {
+  return yh::loss_phases(yh::kPhaseRows, ws, heads, layers, L, B, C, m_batch, m_flat, m_target,
+                         m_class, M_dev, capacity, cfg, losses4_dev, iou_score_dev, pred_rows_dev,
+                         grad_heads, stream);
+}
+
+}  // extern "C"

@@ -60,33 +60,106 @@ class DeviceStep:
         self.conf = torch.empty(self.kcap, dtype=f32, device=device)
         self.K = torch.zeros(1, dtype=i32, device=device)
         self._grad_ptrs = _lib.ptr_array(self.grads) if with_grad else None
+        self._side = None
+        self._graph = None
+        self.kernels_in_graph = 0
 
     def algorithmic_bytes(self):
         """SURVEY.md §8d per-image figures x batch, per kernel (M-dependent part excluded)."""
         n = self.N * self.B
         return {"decode_kernel": 32 * n, "loss_dense_kernel": 344 * n, "nms_filter_kernel": 340 * n}
 
+    KERNELS_PER_STEP = 8
+
     def run(self, heads: Sequence[torch.Tensor], gt_dev: torch.Tensor, off_dev: torch.Tensor, stream=None):
         """heads: L contiguous f32 CUDA tensors [B, A*(5+C), H, W]; gt_dev [G,5] f64; off_dev [B+1] i32.
-        Enqueues 8 kernels on the current stream; nothing synchronises."""
+        Enqueues 8 kernels on ONE stream, in the order the reference executes them; nothing
+        synchronises."""
         s = stream if stream is not None else torch.cuda.current_stream(self.dev).cuda_stream
-        lib, ck = self.lib, _lib.check
-        hp = _lib.ptr_array(heads)
+        self._decode(_lib.ptr_array(heads), s)
+        self._assign(gt_dev, off_dev, s)
+        self._loss(self.lib.yh_loss_fwd_bwd, _lib.ptr_array(heads), s)
+        self._nms(_lib.ptr_array(heads), s)
+
+    # -- the four C-ABI calls ------------------------------------------------------------
+    def _decode(self, hp, s):
         b = self.boxes
-        ck(lib.yh_decode_merged(hp, self.layers, self.L, self.B, self.C, b[0].data_ptr(), b[1].data_ptr(),
-                                b[2].data_ptr(), b[3].data_ptr(), self.N, s))
-        ck(lib.yh_assign(self.ws.handle, gt_dev.data_ptr(), off_dev.data_ptr(), self.B, self.layers, self.L,
-                         self.rect4, self.thresh, self.m_batch.data_ptr(), self.m_flat.data_ptr(),
-                         self.m_gt.data_ptr(), self.m_target.data_ptr(), self.m_class.data_ptr(),
-                         self.M.data_ptr(), self.mcap, s))
-        ck(lib.yh_loss_fwd_bwd(self.ws.handle, hp, self.layers, self.L, self.B, self.C,
-                               self.m_batch.data_ptr(), self.m_flat.data_ptr(), self.m_target.data_ptr(),
-                               self.m_class.data_ptr(), self.M.data_ptr(), self.mcap, self.cfg,
-                               self.losses4.data_ptr(), self.iou_score.data_ptr(), self.pred_rows.data_ptr(),
-                               self._grad_ptrs, s))
-        ck(lib.yh_nms(self.ws.handle, hp, self.layers, self.L, self.B, self.C, self.nms_conf, self.nms_iou,
-                      self.by_class, self.kb.data_ptr(), self.kc.data_ptr(), self.ki.data_ptr(),
-                      self.tlbr.data_ptr(), self.conf.data_ptr(), self.K.data_ptr(), self.kcap, s))
+        _lib.check(self.lib.yh_decode_merged(hp, self.layers, self.L, self.B, self.C, b[0].data_ptr(),
+                                             b[1].data_ptr(), b[2].data_ptr(), b[3].data_ptr(), self.N, s))
+
+    def _assign(self, gt_dev, off_dev, s):
+        _lib.check(self.lib.yh_assign(self.ws.handle, gt_dev.data_ptr(), off_dev.data_ptr(), self.B,
+                                      self.layers, self.L, self.rect4, self.thresh, self.m_batch.data_ptr(),
+                                      self.m_flat.data_ptr(), self.m_gt.data_ptr(), self.m_target.data_ptr(),
+                                      self.m_class.data_ptr(), self.M.data_ptr(), self.mcap, s))
+
+    def _loss(self, fn, hp, s):
+        _lib.check(fn(self.ws.handle, hp, self.layers, self.L, self.B, self.C, self.m_batch.data_ptr(),
+                      self.m_flat.data_ptr(), self.m_target.data_ptr(), self.m_class.data_ptr(),
+                      self.M.data_ptr(), self.mcap, self.cfg, self.losses4.data_ptr(),
+                      self.iou_score.data_ptr(), self.pred_rows.data_ptr(), self._grad_ptrs, s))
+
+    def _nms(self, hp, s):
+        _lib.check(self.lib.yh_nms(self.ws.handle, hp, self.layers, self.L, self.B, self.C, self.nms_conf,
+                                   self.nms_iou, self.by_class, self.kb.data_ptr(), self.kc.data_ptr(),
+                                   self.ki.data_ptr(), self.tlbr.data_ptr(), self.conf.data_ptr(),
+                                   self.K.data_ptr(), self.kcap, s))
+
+    # -- the same 8 kernels as a fork/join over four streams --------------------------------
+    def run_overlapped(self, heads, gt_dev, off_dev):
+        """The step as the dependency graph it really is (the reference runs it as one sequence,
+        train/src/train/single_gpu.rs:152-186):
+
+            decode                                   (Detect2D x L + merge)
+            assign ----------------\
+            loss_dense -------------+--> loss_rows   (YoloLoss fwd+bwd; the dense objectness pass
+            nms_filter -> nms_segment -> nms_emit     needs no matches)
+
+        The four branches are forked from the current stream onto side streams and joined back
+        into it, so the latency-bound kernels (one CTA per image: assignment, greedy NMS) run
+        under the HBM-bound ones (decode, dense loss, candidate filter).  Capturable in a CUDA
+        graph (`capture`)."""
+        main = torch.cuda.current_stream(self.dev)
+        if self._side is None:
+            self._side = [torch.cuda.Stream(self.dev) for _ in range(3)]
+        s_dec, s_asg, s_nms = self._side
+        hp = _lib.ptr_array(heads)
+        fork = torch.cuda.Event()
+        fork.record(main)
+        for st in self._side:
+            st.wait_event(fork)
+        _lib.check(self.lib.yh_loss_dense(self.ws.handle, hp, self.layers, self.L, self.B, self.C, self.cfg,
+                                          self._grad_ptrs, main.cuda_stream))
+        self._assign(gt_dev, off_dev, s_asg.cuda_stream)
+        self._nms(hp, s_nms.cuda_stream)
+        self._decode(hp, s_dec.cuda_stream)
+        joins = []
+        for st in self._side:
+            e = torch.cuda.Event()
+            e.record(st)
+            joins.append(e)
+        main.wait_event(joins[1])
+        self._loss(self.lib.yh_loss_rows, hp, main.cuda_stream)
+        main.wait_event(joins[0])
+        main.wait_event(joins[2])
+
+    def capture(self, heads, gt_dev, off_dev):
+        """Captures `run_overlapped` on these buffers into a CUDA graph; `replay()` launches it.
+        The captured pointers are those of `heads`/`gt_dev`/`off_dev`: refill them in place."""
+        self._keep = (list(heads), gt_dev, off_dev)
+        self.run_overlapped(heads, gt_dev, off_dev)  # warm: module attributes, streams
+        torch.cuda.synchronize(self.dev)
+        g = torch.cuda.CUDAGraph()
+        cap = torch.cuda.Stream(self.dev)
+        before = int(self.lib.yh_launch_count(0))
+        with torch.cuda.graph(g, stream=cap):
+            self.run_overlapped(heads, gt_dev, off_dev)
+        self.kernels_in_graph = int(self.lib.yh_launch_count(0)) - before
+        self._graph = g
+        return g
+
+    def replay(self):
+        self._graph.replay()
 
     def counts(self):
         """synchronising read of (M, K); raises on overflow."""
