@@ -272,32 +272,70 @@ def run_native(args):
                                       "achieved_GBps": (alg[n] / (kern_ms[n] * 1e-3) / 1e9) if n in alg else None}
                                   for n in kern_ms if n != dom}}
 
-    # end to end through host buffers (pinned): H2D heads+labels, step, D2H results + gradients
+    # end to end through host buffers (pinned): every step pays H2D of its heads+labels, the 8
+    # kernels, and D2H of losses + matches + detections + head gradients.  HostPipeline overlaps
+    # step i's compute with step i+1's H2D and step i-1's D2H (2 slots, 3 streams); HostStep (one
+    # stream, nothing overlapped) is timed beside it.
     e2e = None
     if not args.no_e2e:
-        hs = HostStep(spec, B, dev, nms_conf=NMS_CONF, nms_iou=NMS_IOU, by_class=BY_CLASS)
+        from yolo_dl_b200.pipeline import HostPipeline
         host_heads = [h.cpu().pin_memory() for h in heads]
-        Ke = max(3, min(K, 10))
+        Ke = max(4, min(K, 20))
+
+        def timed(fn, finish):
+            barrier()
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0 = time.perf_counter()
+            a0.record()
+            for _ in range(Ke):
+                fn()
+            finish()
+            a1.record()
+            torch.cuda.synchronize()
+            wall = (time.perf_counter() - t0) * 1e3
+            barrier()
+            m = max(wall, a0.elapsed_time(a1))
+            if world > 1:
+                t = torch.tensor([m], device=dev)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                m = float(t)
+            return m
+
+        hs = HostStep(spec, B, dev, nms_conf=NMS_CONF, nms_iou=NMS_IOU, by_class=BY_CLASS)
         for _ in range(2):
             hs.run(host_heads, gt_h, off_h)
-        barrier()
-        t0 = time.perf_counter()
-        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a0.record()
-        for _ in range(Ke):
-            hl, hM, hK = hs.run(host_heads, gt_h, off_h)
-        a1.record()
-        barrier()
-        ems = a0.elapsed_time(a1)
-        if world > 1:
-            t = torch.tensor([ems], device=dev)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ems = float(t)
-        e2e = {"value": world * B * Ke / (ems * 1e-3), "unit": UNIT, "h2d_bytes_per_step": hs.h2d_bytes,
-               "d2h_bytes_per_step": hs.d2h_bytes, "steps": Ke, "ms_per_step": ems / Ke,
-               "includes": "H2D heads+labels, 8 kernels, D2H losses+matches+detections+head gradients",
+        serial_ms = timed(lambda: hs.run(host_heads, gt_h, off_h), lambda: None)
+        del hs
+        pipe = HostPipeline(spec, B, dev, depth=2, nms_conf=NMS_CONF, nms_iou=NMS_IOU, by_class=BY_CLASS)
+        last = {}
+
+        def pstep():
+            k = pipe.submit(host_heads, gt_h, off_h)
+            if "k" in last:          # read the previous step's loss while this one is in flight
+                last["r"] = pipe.result(last["k"])
+                last["loss"] = float(last["r"][0][0])
+            last["k"] = k
+
+        def pfinish():
+            last["r"] = pipe.result(last["k"])
+            last["loss"] = float(last["r"][0][0])
+            pipe.drain()
+
+        for _ in range(3):
+            pstep()
+        pfinish()
+        last.clear()
+        ems = timed(pstep, pfinish)
+        hl, hM, hK = last["r"]
+        e2e = {"value": world * B * Ke / (ems * 1e-3), "unit": UNIT, "h2d_bytes_per_step": pipe.h2d_bytes,
+               "d2h_bytes_per_step": pipe.d2h_bytes, "steps": Ke, "ms_per_step": ems / Ke,
+               "includes": "per step: H2D heads+labels, 8 kernels (graph), D2H losses+matches+detections+head "
+                           "gradients; 2-slot pipeline over copy-in/compute/copy-out streams; timed by "
+                           "max(wall clock, CUDA events) around the loop incl. the final drain",
+               "unpipelined_ms_per_step": serial_ms / Ke,
+               "pcie_GBps_each_way": [pipe.h2d_bytes / (ems / Ke) / 1e6, pipe.d2h_bytes / (ems / Ke) / 1e6],
                "loss": float(hl[0]), "matches": hM, "detections": hK}
-        del hs, host_heads
+        del pipe, host_heads
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

@@ -130,3 +130,43 @@ def test_host_step_round_trip(dev):
     for g, r in zip(hs.h_grads, ref["grads"]):
         grad_close(g, r, what="grad")
     assert hs.h2d_bytes > 0 and hs.d2h_bytes > 0
+
+
+def test_host_pipeline_overlapped_slots(dev):
+    """Results of the 2-slot pipeline equal the unpipelined HostStep for a stream of different batches."""
+    from yolo_dl_b200.pipeline import HostPipeline
+    spec = synth.small_spec()
+    B = 4
+    batches = []
+    for seed in range(5):
+        heads = [h.pin_memory() for h in synth.make_heads(spec, B, 100 + seed, obj_mean=-1.0, cls_mean=-1.0)]
+        gt, off = yh.pack_labels(synth.make_targets(spec, B, 100 + seed, n_max=6))
+        batches.append((heads, gt, off))
+    hs = HostStep(spec, B, dev, nms_conf=0.3)
+    want = []
+    for heads, gt, off in batches:
+        losses, M, K = hs.run(heads, gt, off)
+        want.append((losses.clone(), M, K, hs.h_match[:, :M].clone(), hs.h_det[:, :K].clone(),
+                     [g.clone() for g in hs.h_grads]))
+    pipe = HostPipeline(spec, B, dev, depth=2, nms_conf=0.3)
+    slots = []
+    got = []
+
+    def collect(k):
+        losses, M, K = pipe.result(k)
+        s = pipe.slots[k]
+        got.append((losses.clone(), M, K, s.h_match[:, :M].clone(), s.h_det[:, :K].clone(),
+                    [g.clone() for g in s.h_grads]))
+
+    for i, (heads, gt, off) in enumerate(batches):
+        if i >= 2:
+            collect(slots[i - 2])  # a slot's results must be read before it is reused
+        slots.append(pipe.submit(heads, gt, off))
+    collect(slots[-2])
+    collect(slots[-1])
+    assert len(got) == len(want)
+    for g, w in zip(got, want):
+        assert torch.equal(g[0], w[0]) and g[1] == w[1] and g[2] == w[2]
+        assert torch.equal(g[3], w[3]) and torch.equal(g[4], w[4])
+        for x, y in zip(g[5], w[5]):
+            assert torch.equal(x, y)

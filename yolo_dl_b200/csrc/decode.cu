@@ -4,106 +4,99 @@
 //
 // HBM-bound streaming kernel: per instance it reads the 4 box logits (entries 0..3 of the
 // entry-major head, each a unit-stride run along the cell index) and writes cy,cx,h,w.
-// Algorithmic traffic 32 B per instance.  One thread handles QUAD=4
-// consecutive flat indices: where the four share (layer, anchor) and the addresses are
-// 16-byte aligned it uses one float4 load per entry and one float4 store per output,
-// otherwise (19x19 / 13x13 maps, odd batch strides) it falls back to scalar accesses that
-// are still coalesced across the warp.
+// Algorithmic traffic 32 B per instance.  The four outputs are independent
+// functions of one logit each (cy of entry 0, cx of 1, h of 2, w of 3), so the grid is
+// (chunks, B, 4 entries) where a chunk is kDecodeThreads*4 consecutive cells of ONE
+// (layer, anchor) plane: a CTA never straddles planes, so there is no per-thread search for
+// the layer, the entry is block-uniform (one instantiation per entry), and the grid term
+// arange(size)/size of detect_2d.rs:122-133 is a <= 1024-entry table built once per CTA in
+// shared memory (the reference caches the same table per (H,W), detect_2d.rs:162-238).
+// A thread: one 16-byte load, four sigmoids, one 16-byte store.  19x19 / 13x13 planes and odd
+// batch strides are not 16-byte aligned: those use scalar accesses, still coalesced.
 #include "common.cuh"
 
 namespace yh {
 
 constexpr int kDecodeThreads = 256;
+constexpr int kDecodeChunk = kDecodeThreads * 4;
+constexpr int kGridTabMax = 1024;
 
-__device__ __forceinline__ void decode_one(const LayerTab& t, int l, int anchor, int row,
-                                           int col, float x0, float x1, float x2, float x3,
-                                           float& cy, float& cx, float& h, float& w) {
-  cy = decode_center(sigmoid_f(x0), row, (float)t.H[l]);
-  cx = decode_center(sigmoid_f(x1), col, (float)t.W[l]);
-  h = decode_size(sigmoid_f(x2), t.ah[l][anchor]);
-  w = decode_size(sigmoid_f(x3), t.aw[l][anchor]);
+struct ChunkTab {
+  int cpp[YH_MAX_LAYERS];     // chunks per (layer, anchor) plane
+  int cstart[YH_MAX_LAYERS];  // first chunk of the layer
+};
+
+template <int E>
+__device__ __forceinline__ void decode_plane(const LayerTab& t, const ChunkTab& ct,
+                                             float* __restrict__ outp, long long out_stride,
+                                             float* s_tab) {
+  const int b = blockIdx.y;
+  int l = 0;
+#pragma unroll
+  for (int i = 1; i < YH_MAX_LAYERS; ++i)
+    if (i < t.L && (int)blockIdx.x >= ct.cstart[i]) l = i;
+  const int rel = blockIdx.x - ct.cstart[l];
+  const int anchor = rel / ct.cpp[l];
+  const int chunk = rel - anchor * ct.cpp[l];
+  const int H = t.H[l], W = t.W[l], HW = t.HW[l];
+  const float size = (E == 0) ? (float)H : (float)W;
+  const int tab_n = (E == 0) ? H : W;
+  const bool use_tab = E < 2 && tab_n <= kGridTabMax;
+  if (use_tab) {
+    for (int i = threadIdx.x; i < tab_n; i += kDecodeThreads) s_tab[i] = (float)i / size;
+    __syncthreads();
+  }
+  const int cell0 = chunk * kDecodeChunk + threadIdx.x * 4;
+  if (cell0 >= HW) return;
+  const float anc = (E == 2) ? t.ah[l][anchor] : t.aw[l][anchor];
+  const float* __restrict__ p =
+      t.head[l] + ((size_t)b * (size_t)(t.A[l] * t.E) + (size_t)(E * t.A[l] + anchor)) * (size_t)HW + cell0;
+  float* __restrict__ out =
+      outp + (size_t)b * (size_t)out_stride + (size_t)t.start[l] + (size_t)anchor * HW + cell0;
+  int row = cell0 / W, col = cell0 - row * W;
+  const int cnt = min(4, HW - cell0);
+
+  float a[4] = {0.f, 0.f, 0.f, 0.f};
+  if (cnt == 4 && ((uintptr_t)p & 15) == 0) {
+    const float4 v = __ldcs(reinterpret_cast<const float4*>(p));
+    a[0] = v.x; a[1] = v.y; a[2] = v.z; a[3] = v.w;
+  } else {
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      if (i < cnt) a[i] = __ldcs(p + i);
+  }
+  float o[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float s = sigmoid_f(a[i]);
+    if (E < 2) {
+      const int idx = (E == 0) ? row : col;
+      // (sigmoid*2 - 0.5)/size + arange(size)[idx]/size   == decode_center()
+      const float g = use_tab ? s_tab[idx] : (float)idx / size;
+      o[i] = (s * 2.0f - 0.5f) / size + g;
+      if (++col == W) { col = 0; ++row; }
+    } else {
+      o[i] = decode_size(s, anc);
+    }
+  }
+  if (cnt == 4 && ((uintptr_t)out & 15) == 0) {
+    st_stream4(reinterpret_cast<float4*>(out), make_float4(o[0], o[1], o[2], o[3]));
+  } else {
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      if (i < cnt) st_stream1(out + i, o[i]);
+  }
 }
 
 __global__ void __launch_bounds__(kDecodeThreads)
-decode_kernel(const LayerTab t, float* __restrict__ cy, float* __restrict__ cx,
+decode_kernel(const LayerTab t, const ChunkTab ct, float* __restrict__ cy, float* __restrict__ cx,
               float* __restrict__ h, float* __restrict__ w, long long out_stride) {
-  const int b = blockIdx.y;
-  const int n0 = (blockIdx.x * kDecodeThreads + threadIdx.x) * 4;
-  if (n0 >= t.N) return;
-  const size_t ob = (size_t)b * (size_t)out_stride + (size_t)n0;
-
-  const Cell c0 = locate(t, n0);
-  const int l = c0.layer;
-  const size_t estride = (size_t)t.A[l] * (size_t)t.HW[l];
-  const float* p = t.head[l] + head_offset(t, l, b, c0.anchor, c0.cell);
-  const bool same = (n0 + 3 < t.N) && (c0.cell + 3 < t.HW[l]);
-  const bool in_al = (((uintptr_t)p | (uintptr_t)(estride * sizeof(float))) & 15) == 0;
-
-  if (same && in_al) {
-    const float4 v0 = __ldcs(reinterpret_cast<const float4*>(p));
-    const float4 v1 = __ldcs(reinterpret_cast<const float4*>(p + estride));
-    const float4 v2 = __ldcs(reinterpret_cast<const float4*>(p + 2 * estride));
-    const float4 v3 = __ldcs(reinterpret_cast<const float4*>(p + 3 * estride));
-    const float a0[4] = {v0.x, v0.y, v0.z, v0.w};
-    const float a1[4] = {v1.x, v1.y, v1.z, v1.w};
-    const float a2[4] = {v2.x, v2.y, v2.z, v2.w};
-    const float a3[4] = {v3.x, v3.y, v3.z, v3.w};
-    float ocy[4], ocx[4], oh[4], ow[4];
-    int row = c0.row, col = c0.col;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      decode_one(t, l, c0.anchor, row, col, a0[i], a1[i], a2[i], a3[i], ocy[i], ocx[i], oh[i],
-                 ow[i]);
-      if (++col == t.W[l]) { col = 0; ++row; }
-    }
-    const bool out_al = (((uintptr_t)(cy + ob) | (uintptr_t)(cx + ob) | (uintptr_t)(h + ob) |
-                          (uintptr_t)(w + ob)) & 15) == 0;
-    if (out_al) {
-      st_stream4(reinterpret_cast<float4*>(cy + ob), make_float4(ocy[0], ocy[1], ocy[2], ocy[3]));
-      st_stream4(reinterpret_cast<float4*>(cx + ob), make_float4(ocx[0], ocx[1], ocx[2], ocx[3]));
-      st_stream4(reinterpret_cast<float4*>(h + ob), make_float4(oh[0], oh[1], oh[2], oh[3]));
-      st_stream4(reinterpret_cast<float4*>(w + ob), make_float4(ow[0], ow[1], ow[2], ow[3]));
-    } else {
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        st_stream1(cy + ob + i, ocy[i]);
-        st_stream1(cx + ob + i, ocx[i]);
-        st_stream1(h + ob + i, oh[i]);
-        st_stream1(w + ob + i, ow[i]);
-      }
-    }
-    return;
-  }
-
-  // generic path: each of the (up to) four instances located on its own
-  float x[4][4];
-  Cell cs[4];
-  int cnt = 0;
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    if (n0 + i < t.N) {
-      cs[i] = locate(t, n0 + i);
-      const int li = cs[i].layer;
-      const size_t es = (size_t)t.A[li] * (size_t)t.HW[li];
-      const float* q = t.head[li] + head_offset(t, li, b, cs[i].anchor, cs[i].cell);
-      x[i][0] = __ldcs(q);
-      x[i][1] = __ldcs(q + es);
-      x[i][2] = __ldcs(q + 2 * es);
-      x[i][3] = __ldcs(q + 3 * es);
-      cnt = i + 1;
-    }
-  }
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    if (i < cnt) {
-      float ocy, ocx, oh, ow;
-      decode_one(t, cs[i].layer, cs[i].anchor, cs[i].row, cs[i].col, x[i][0], x[i][1], x[i][2],
-                 x[i][3], ocy, ocx, oh, ow);
-      st_stream1(cy + ob + i, ocy);
-      st_stream1(cx + ob + i, ocx);
-      st_stream1(h + ob + i, oh);
-      st_stream1(w + ob + i, ow);
-    }
+  __shared__ float s_tab[kGridTabMax];
+  switch (blockIdx.z) {  // block-uniform
+    case 0: decode_plane<0>(t, ct, cy, out_stride, s_tab); break;
+    case 1: decode_plane<1>(t, ct, cx, out_stride, s_tab); break;
+    case 2: decode_plane<2>(t, ct, h, out_stride, s_tab); break;
+    default: decode_plane<3>(t, ct, w, out_stride, s_tab); break;
   }
 }
 
@@ -113,10 +106,16 @@ static int launch_decode(const LayerTab& tab, int B, float* cy, float* cx, float
   YH_REQUIRE(cy && cx && h && w, "output pointer is NULL");
   YH_REQUIRE(out_stride >= tab.N, "out_batch_stride=%lld < instances %d", (long long)out_stride,
              tab.N);
-  const int quads = (tab.N + 3) / 4;
-  dim3 grid((quads + kDecodeThreads - 1) / kDecodeThreads, B);
+  ChunkTab ct;
+  int chunks = 0;
+  for (int l = 0; l < YH_MAX_LAYERS; ++l) {
+    ct.cpp[l] = l < tab.L ? (tab.HW[l] + kDecodeChunk - 1) / kDecodeChunk : 1;
+    ct.cstart[l] = chunks;
+    if (l < tab.L) chunks += ct.cpp[l] * tab.A[l];
+  }
+  dim3 grid(chunks, B, 4);
   YH_TIME(YH_K_DECODE, s);
-  decode_kernel<<<grid, kDecodeThreads, 0, s>>>(tab, cy, cx, h, w, (long long)out_stride);
+  decode_kernel<<<grid, kDecodeThreads, 0, s>>>(tab, ct, cy, cx, h, w, (long long)out_stride);
   YH_LAUNCHED(s);
   return YH_OK;
 }

@@ -16,8 +16,8 @@
 // It is a pure streaming kernel: float4 stores over the flat gradient tensor of each layer
 // (the tensor is contiguous, so the flat view is 16-byte aligned even for 19x19 maps whose
 // channel rows are not).
-// K3: one warp per matched row, lanes across the C class channels; the 5+C logits of a row
-// are (5+C) scattered 4-byte reads, M is small (10..15 per GT box).
+// K3: a warp per 8 matched rows (scalar box part one row per lane, class part lanes across the
+// C channels); the 5+C logits of a row are (5+C) scattered 4-byte reads, M is 10..15 per GT.
 //
 // Reductions are deterministic: per-CTA partials in fixed slots, summed in a fixed order by
 // the last CTA of K3 (ticket counter), in f64.
@@ -28,7 +28,7 @@
 namespace yh {
 
 constexpr int kDenseThreads = 256;
-constexpr int kRowThreads = 256;
+constexpr int kRowThreads = 128;
 constexpr int kPartHalf = YH_PARTIALS_MAX / 2;  // K4 partials in [0,kPartHalf), K3 after
 
 struct GradTab {
@@ -61,7 +61,10 @@ __device__ __forceinline__ float softplus_f(float x) {
 //     stores per thread — no loads, no address arithmetic beyond an immediate offset.
 //     tools/fill_bench.cu measured this form at 6.0-6.3 TB/s on B200 (cudaMemset: 6.6-6.8),
 //     level with TMA bulk stores from a zeroed shared buffer, so the simpler form is used;
-//   * it does: per-quad classification with a single conditional wrap instead of a modulo.
+//   * it does: per-quad test with a single conditional wrap instead of a modulo; the quads
+//     that hold an objectness element are NOT written here but by pass 1, which spreads all
+//     B*N/4 of them evenly over the grid (left in the tiles they serialise a few CTAs on
+//     load latency + transcendental math while the others have long finished: 97 -> ~85 us).
 constexpr int kTileUnroll = 8;
 constexpr int kTileQuads = kDenseThreads * kTileUnroll;  // 2048 quads = 8192 floats = 32 KB
 constexpr int kTileFloats = kTileQuads * 4;
@@ -72,6 +75,68 @@ loss_dense_kernel(const LayerTab t, const GradTab g, const int B, const float nu
                   const float w_obj, const int reduction, double* __restrict__ partials) {
   double acc = 0.0;
   if (GRAD) {
+    // ---- pass 1: the quads that hold at least one objectness element ---------------------
+    // (B*N/4 of them, spread evenly over the whole grid so that their load latency and
+    // transcendental math are paid in parallel, before the store stream starts).  Slot j of
+    // image b of layer l is quad floor((b*per_img + 4*run)/4) + j, if it still starts before
+    // the plane's end.
+    {
+      long long qprefix[YH_MAX_LAYERS + 1];
+      qprefix[0] = 0;
+#pragma unroll
+      for (int l = 0; l < YH_MAX_LAYERS; ++l)
+        qprefix[l + 1] = qprefix[l] + ((l < t.L) ? (long long)B * ((t.A[l] * t.HW[l]) / 4 + 2) : 0LL);
+      const long long total = qprefix[YH_MAX_LAYERS];
+      const long long stride = (long long)gridDim.x * kDenseThreads;
+      for (long long i = (long long)blockIdx.x * kDenseThreads + threadIdx.x; i < total; i += stride) {
+        int l = 0;
+#pragma unroll
+        for (int k = 1; k < YH_MAX_LAYERS; ++k)
+          if (k < t.L && i >= qprefix[k]) l = k;
+        const int run = t.A[l] * t.HW[l];
+        const int slots = run / 4 + 2;
+        const long long li = i - qprefix[l];
+        const long long b = li / slots;
+        const int j = (int)(li - b * slots);
+        const long long per_img = (long long)run * t.E;
+        const long long len = (long long)B * per_img;
+        const long long o0 = b * per_img + 4LL * run, o1 = o0 + run;  // obj plane of image b
+        const long long idx = (o0 / 4 + j) * 4;                        // first float of the quad
+        if (idx >= o1) continue;
+        const float* __restrict__ hp = t.head[l] + idx;
+        float* __restrict__ gp = g.grad[l] + idx;
+        const bool full = idx + 3 < len;
+        float x[4] = {0.f, 0.f, 0.f, 0.f};
+        if (idx >= o0 && idx + 3 < o1) {
+          const float4 v = __ldcs(reinterpret_cast<const float4*>(hp));
+          x[0] = v.x; x[1] = v.y; x[2] = v.z; x[3] = v.w;
+        } else {
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            if (idx + k >= o0 && idx + k < o1) x[k] = __ldcs(hp + k);
+        }
+        float v[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          if (idx + k >= o0 && idx + k < o1) {
+            acc += (double)softplus_f(x[k]);
+            // BCE backward, target 0: sigmoid(x) [/numel for Mean] * upstream w_obj
+            float gi = sigmoid_f(x[k]);
+            if (reduction == YH_REDUCTION_MEAN) gi = gi / numel;
+            v[k] = gi * w_obj;
+          }
+        }
+        if (full) {
+          st_stream4(reinterpret_cast<float4*>(gp), make_float4(v[0], v[1], v[2], v[3]));
+        } else {
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            if (idx + k < len) st_stream1(gp + k, v[k]);
+        }
+      }
+    }
+
+    // ---- pass 2: zeros everywhere else -------------------------------------------------------
     long long prefix[YH_MAX_LAYERS + 1];  // in tiles
     prefix[0] = 0;
 #pragma unroll
@@ -94,7 +159,9 @@ loss_dense_kernel(const LayerTab t, const GradTab g, const int B, const float nu
       const long long per_img = run * t.E;                // floats per image
       const long long len = (long long)B * per_img;
       const long long idx0 = (tile - prefix[l]) * kTileFloats;  // first float of the tile
-      const long long r0 = idx0 % per_img;                      // its offset inside the image
+      // its offset inside the image (32-bit modulo whenever the layer tensor allows it)
+      const long long r0 = (len < (1LL << 31)) ? (long long)((unsigned)idx0 % (unsigned)per_img)
+                                               : idx0 % per_img;
       const long long o0 = 4 * run, o1 = 5 * run;               // obj plane of an image
       float* __restrict__ gbase = g.grad[l] + idx0;
       const bool whole = idx0 + kTileFloats <= len;
@@ -107,8 +174,9 @@ loss_dense_kernel(const LayerTab t, const GradTab g, const int B, const float nu
         for (int u = 0; u < kTileUnroll; ++u) st_stream4(q + u * kDenseThreads, zero4);
         continue;
       }
-      const float* __restrict__ hbase = t.head[l] + idx0;
-#pragma unroll 2
+      // a tile that meets an objectness plane or the end of the tensor: per-quad test, quads
+      // with an objectness element belong to pass 1
+#pragma unroll
       for (int u = 0; u < kTileUnroll; ++u) {
         const int qi = u * kDenseThreads + threadIdx.x;
         const long long idx = idx0 + 4LL * qi;
@@ -119,35 +187,15 @@ loss_dense_kernel(const LayerTab t, const GradTab g, const int B, const float nu
         } else {
           r %= per_img;
         }
-        const bool full = idx + 3 < len;
         const bool hit = (r + 3 >= o0 && r < o1) || (r + 3 >= per_img + o0);
+        if (hit) continue;
         float* gp = gbase + 4 * qi;
-        if (full && !hit) {
+        if (idx + 3 < len) {
           st_stream4(reinterpret_cast<float4*>(gp), zero4);
-          continue;
-        }
-        float v[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          if (idx + k < len) {
-            long long rk = r + k;
-            if (rk >= per_img) rk -= per_img;
-            if (rk >= o0 && rk < o1) {
-              const float x = __ldcs(hbase + 4 * qi + k);
-              acc += (double)softplus_f(x);
-              // BCE backward, target 0: sigmoid(x) [/numel for Mean] * upstream w_obj
-              float gi = sigmoid_f(x);
-              if (reduction == YH_REDUCTION_MEAN) gi = gi / numel;
-              v[k] = gi * w_obj;
-            }
-          }
-        }
-        if (full) {
-          st_stream4(reinterpret_cast<float4*>(gp), make_float4(v[0], v[1], v[2], v[3]));
         } else {
 #pragma unroll
           for (int k = 0; k < 4; ++k)
-            if (idx + k < len) st_stream1(gp + k, v[k]);
+            if (idx + k < len) st_stream1(gp + k, 0.0f);
         }
       }
     }
@@ -313,6 +361,16 @@ __device__ __forceinline__ float box_metric(const int metric, const Box4 p, cons
 // ---------------------------------------------------------------------------------
 // K3
 // ---------------------------------------------------------------------------------
+// A warp owns kRowsPerWarp consecutive matched rows.
+//   phase A  lane r < kRowsPerWarp owns row m0+r: index loads, cell location, the five leading
+//            logits, decode, box metric forward + reverse, objectness correction — the ~900
+//            instruction scalar part is paid once per kRowsPerWarp rows, not once per row;
+//   phase B  the whole warp walks the rows: lanes across the C class channels (three per lane
+//            up to C = 96, the rest in a tail loop), class BCE forward + backward.
+// Every load of both phases is issued before the first value is consumed.
+constexpr int kRowsPerWarp = 8;
+constexpr int kClsRegs = 3;
+
 __global__ void __launch_bounds__(kRowThreads)
 loss_rows_kernel(const LayerTab t, const GradTab g, const LossParams p,
                  const long long* __restrict__ m_batch, const long long* __restrict__ m_flat,
@@ -329,70 +387,71 @@ loss_rows_kernel(const LayerTab t, const GradTab g, const LossParams p,
   const float MCf = (float)((long long)M * t.C);
   const float numel_obj = (float)((long long)p.B * t.N);
 
-  double a_iou = 0.0, a_cls = 0.0, a_obj = 0.0;  // lane 0 of each warp accumulates
+  double a_iou = 0.0, a_cls = 0.0, a_obj = 0.0;
 
-  for (int m = blockIdx.x * warps + wid; m < M; m += gridDim.x * warps) {
-    const int b = (int)m_batch[m];
-    const int flat = (int)m_flat[m];
-    const Cell c = locate(t, flat);
-    const int l = c.layer;
-    const size_t es = (size_t)t.A[l] * (size_t)t.HW[l];
-    const size_t off = head_offset(t, l, b, c.anchor, c.cell);
-    const float* hp = t.head[l] + off;
-    float* gp = want_grad ? g.grad[l] + off : nullptr;
-
-    // every load of the row is issued before anything is consumed: lanes 0..4 fetch the five
-    // leading logits (then broadcast by shuffle), every lane its first three class logits
-    const float xl = (lane < 5) ? hp[(size_t)lane * es] : 0.0f;
-    float xc[3];
+  for (int m0 = (blockIdx.x * warps + wid) * kRowsPerWarp; m0 < M;
+       m0 += gridDim.x * warps * kRowsPerWarp) {
+    // ---- phase A, part 1: where is my row -------------------------------------------
+    const int m = m0 + lane;
+    const bool own = lane < kRowsPerWarp && m < M;
+    long long off = 0;     // offset of entry 0 of the row inside its head tensor
+    int es = 0, l = 0, cls = 0, anchor = 0, row = 0, col = 0;
+    float4 tg = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (own) {
+      const int b = (int)m_batch[m];
+      const int flat = (int)m_flat[m];
+      cls = (int)m_class[m];
+      tg = *reinterpret_cast<const float4*>(m_target + (size_t)m * 4);
+      const Cell c = locate(t, flat);
+      l = c.layer;
+      anchor = c.anchor;
+      row = c.row;
+      col = c.col;
+      es = t.A[l] * t.HW[l];
+      off = (long long)head_offset(t, l, b, c.anchor, c.cell);
+    }
+    // ---- all loads ----------------------------------------------------------------------
+    float xb[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+    if (own) {
+      const float* hp = t.head[l] + off;
 #pragma unroll
-    for (int j = 0; j < 3; ++j) {
-      const int k = lane + 32 * j;
-      xc[j] = (k < t.C) ? hp[(size_t)(5 + k) * es] : 0.0f;
+      for (int e = 0; e < 5; ++e) xb[e] = hp[(size_t)e * es];
     }
-    const float x0 = __shfl_sync(0xffffffffu, xl, 0), x1 = __shfl_sync(0xffffffffu, xl, 1);
-    const float x2 = __shfl_sync(0xffffffffu, xl, 2), x3 = __shfl_sync(0xffffffffu, xl, 3);
-    const float xo = __shfl_sync(0xffffffffu, xl, 4);
-    const float s0 = sigmoid_f(x0), s1 = sigmoid_f(x1), s2 = sigmoid_f(x2), s3 = sigmoid_f(x3);
-    Box4 pb;
-    pb.cy = decode_center(s0, c.row, (float)t.H[l]);
-    pb.cx = decode_center(s1, c.col, (float)t.W[l]);
-    pb.h = decode_size(s2, t.ah[l][c.anchor]);
-    pb.w = decode_size(s3, t.aw[l][c.anchor]);
-    Box4 tb;
-    tb.cy = m_target[(size_t)m * 4 + 0];
-    tb.cx = m_target[(size_t)m * 4 + 1];
-    tb.h = m_target[(size_t)m * 4 + 2];
-    tb.w = m_target[(size_t)m * 4 + 3];
-
-    // d total / d metric: total = w_iou * mean(1 - metric)
-    float gm = p.w_iou;
-    if (p.reduction == YH_REDUCTION_MEAN) gm = gm / Mf;
-    gm = -gm;
-    Box4 d = {0.f, 0.f, 0.f, 0.f};
-    const float metric = box_metric(p.metric, pb, tb, gm, want_grad, d);
-
-    // class BCE over C channels, lanes strided
-    const int cls = (int)m_class[m];
-    float bce = 0.f;
-    for (int k = lane, j = 0; k < t.C; k += 32, ++j) {
-      const float x = (j < 3) ? xc[j < 3 ? j : 0] : hp[(size_t)(5 + k) * es];
-      const float tt = (k == cls) ? p.cls_pos : p.cls_neg;
-      bce += (1.0f - tt) * x + softplus_f(-x);
-      if (want_grad) {
-        float gi = sigmoid_f(x) - tt;
-        if (p.reduction == YH_REDUCTION_MEAN) gi = gi / MCf;
-        gp[(size_t)(5 + k) * es] = gi * p.w_cls;
+    float xc[kRowsPerWarp][kClsRegs];
+#pragma unroll
+    for (int r = 0; r < kRowsPerWarp; ++r) {
+      const long long off_r = __shfl_sync(0xffffffffu, off, r);
+      const int es_r = __shfl_sync(0xffffffffu, es, r);
+      const int l_r = __shfl_sync(0xffffffffu, l, r);
+      const float* hp = t.head[l_r] + off_r;
+#pragma unroll
+      for (int j = 0; j < kClsRegs; ++j) {
+        const int k = lane + 32 * j;
+        xc[r][j] = (m0 + r < M && k < t.C) ? hp[(size_t)(5 + k) * es_r] : 0.0f;
       }
-      if (pred_rows) pred_rows[(size_t)m * t.E + 5 + k] = x;
     }
-    bce = warp_sum(bce);
 
-    if (lane == 0) {
+    // ---- phase A, part 2: box metric, objectness correction, their gradients ----------
+    if (own) {
+      const float s0 = sigmoid_f(xb[0]), s1 = sigmoid_f(xb[1]);
+      const float s2 = sigmoid_f(xb[2]), s3 = sigmoid_f(xb[3]);
+      const float xo = xb[4];
+      Box4 pb;
+      pb.cy = decode_center(s0, row, (float)t.H[l]);
+      pb.cx = decode_center(s1, col, (float)t.W[l]);
+      pb.h = decode_size(s2, t.ah[l][anchor]);
+      pb.w = decode_size(s3, t.aw[l][anchor]);
+      Box4 tb;
+      tb.cy = tg.x; tb.cx = tg.y; tb.h = tg.z; tb.w = tg.w;
+      // d total / d metric: total = w_iou * mean(1 - metric)
+      float gm = p.w_iou;
+      if (p.reduction == YH_REDUCTION_MEAN) gm = gm / Mf;
+      gm = -gm;
+      Box4 d = {0.f, 0.f, 0.f, 0.f};
+      const float metric = box_metric(p.metric, pb, tb, gm, want_grad, d);
       a_iou += (double)(1.0f - metric);
-      a_cls += (double)bce;
       // objectness target at this cell (loss_.rs:397-406)
-      float to = p.obj_base + fminf(fmaxf(metric, 0.0f), 1.0f) * p.obj_coef;
+      const float to = p.obj_base + fminf(fmaxf(metric, 0.0f), 1.0f) * p.obj_coef;
       const float lwm1 = p.has_pw ? (p.pw - 1.0f) * to : 0.0f;
       a_obj += (double)(-to * xo) + (double)(lwm1 * softplus_f(-xo));
       if (iou_score) iou_score[m] = metric;
@@ -401,14 +460,15 @@ loss_rows_kernel(const LayerTab t, const GradTab g, const LossParams p,
         r[0] = pb.cy; r[1] = pb.cx; r[2] = pb.h; r[3] = pb.w; r[4] = xo;
       }
       if (want_grad) {
+        float* gp = g.grad[l] + off;
         // chain through the decode (detect_2d.rs:69-72,122-133):
         //   cy = (2s-0.5)/H + off  -> dcy/ds = 2/H ; s' = s(1-s)
         //   h  = (2s)^2 * a        -> dh/ds  = a * 2*(2s) * 2
         const float Hf = (float)t.H[l], Wf = (float)t.W[l];
         gp[0] = (d.cy / Hf * 2.0f) * ((1.0f - s0) * s0);
         gp[es] = (d.cx / Wf * 2.0f) * ((1.0f - s1) * s1);
-        gp[2 * es] = ((d.h * t.ah[l][c.anchor]) * (2.0f * (s2 * 2.0f)) * 2.0f) * ((1.0f - s2) * s2);
-        gp[3 * es] = ((d.w * t.aw[l][c.anchor]) * (2.0f * (s3 * 2.0f)) * 2.0f) * ((1.0f - s3) * s3);
+        gp[2 * (size_t)es] = ((d.h * t.ah[l][anchor]) * (2.0f * (s2 * 2.0f)) * 2.0f) * ((1.0f - s2) * s2);
+        gp[3 * (size_t)es] = ((d.w * t.aw[l][anchor]) * (2.0f * (s3 * 2.0f)) * 2.0f) * ((1.0f - s3) * s3);
         // objectness gradient with the real target (overwrites K4's target-0 value)
         const float so = sigmoid_f(xo);
         float gi;
@@ -419,10 +479,43 @@ loss_rows_kernel(const LayerTab t, const GradTab g, const LossParams p,
           gi = so - to;
         }
         if (p.reduction == YH_REDUCTION_MEAN) gi = gi / numel_obj;
-        gp[4 * es] = gi * p.w_obj;
+        gp[4 * (size_t)es] = gi * p.w_obj;
       }
     }
+
+    // ---- phase B: class BCE over C channels, lanes strided ------------------------------
+#pragma unroll
+    for (int r = 0; r < kRowsPerWarp; ++r) {
+      const long long off_r = __shfl_sync(0xffffffffu, off, r);
+      const int es_r = __shfl_sync(0xffffffffu, es, r);
+      const int l_r = __shfl_sync(0xffffffffu, l, r);
+      const int cls_r = __shfl_sync(0xffffffffu, cls, r);
+      if (m0 + r >= M) break;  // warp-uniform
+      const float* hp = t.head[l_r] + off_r;
+      float* gp = want_grad ? g.grad[l_r] + off_r : nullptr;
+      float bce = 0.f;
+      for (int k = lane, j = 0; k < t.C; k += 32, ++j) {
+        float x;
+        if (j == 0) x = xc[r][0];
+        else if (j == 1) x = xc[r][1];
+        else if (j == 2) x = xc[r][2];
+        else x = hp[(size_t)(5 + k) * es_r];
+        const float tt = (k == cls_r) ? p.cls_pos : p.cls_neg;
+        bce += (1.0f - tt) * x + softplus_f(-x);
+        if (want_grad) {
+          float gi = sigmoid_f(x) - tt;
+          if (p.reduction == YH_REDUCTION_MEAN) gi = gi / MCf;
+          gp[(size_t)(5 + k) * es_r] = gi * p.w_cls;
+        }
+        if (pred_rows) pred_rows[(size_t)(m0 + r) * t.E + 5 + k] = x;
+      }
+      bce = warp_sum(bce);
+      a_cls += (double)bce;  // identical in every lane; lane 0's copy is used
+    }
   }
+  // rows were owned by lanes 0..kRowsPerWarp-1: fold them into lane 0 in a fixed order
+  a_iou = warp_sum_d(a_iou);
+  a_obj = warp_sum_d(a_obj);
 
   // CTA partials -> fixed slot
   __shared__ double s_acc[kRowThreads / 32][3];
@@ -518,6 +611,7 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
   if (phases & kPhaseRows) {
     YH_REQUIRE(losses4_dev != nullptr && M_dev != nullptr, "NULL argument");
     YH_REQUIRE(capacity == 0 || (m_batch && m_flat && m_target && m_class), "match list is NULL");
+    YH_REQUIRE(((uintptr_t)m_target & 15) == 0, "m_target not 16-byte aligned");
   }
   YH_REQUIRE(B >= 1 && B <= ws->max_batch, "B=%d outside 1..max_batch=%d", B, ws->max_batch);
   LayerTab tab;
@@ -547,6 +641,7 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
     for (int l = 0; l < L; ++l) {
       YH_REQUIRE(grad_heads[l] != nullptr, "grad_heads[%d] is NULL", l);
       YH_REQUIRE(((uintptr_t)grad_heads[l] & 15) == 0, "grad_heads[%d] not 16-byte aligned", l);
+      YH_REQUIRE(((uintptr_t)heads[l] & 15) == 0, "heads[%d] not 16-byte aligned", l);
       g.grad[l] = grad_heads[l];
     }
   }
@@ -583,7 +678,8 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
   if (phases & kPhaseDense) YH_LAUNCHED(s);
   if (!(phases & kPhaseRows)) return YH_OK;
   int row_grid = kPartHalf;  // one warp per matched row where the partial slots allow
-  const int need = (capacity + (kRowThreads / 32) - 1) / (kRowThreads / 32);
+  const int rows_per_cta = (kRowThreads / 32) * kRowsPerWarp;
+  const int need = (capacity + rows_per_cta - 1) / rows_per_cta;
   if (row_grid > need) row_grid = need;
   if (row_grid < 1) row_grid = 1;
   if (row_grid > kPartHalf) row_grid = kPartHalf;

@@ -191,22 +191,9 @@ class HostStep:
         self.h2d_bytes = 0
         self.d2h_bytes = 0
 
-    def run(self, host_heads: Sequence[torch.Tensor], gt_host: torch.Tensor, off_host: torch.Tensor):
-        """host_heads / gt_host / off_host: pinned host tensors.  Returns (losses4, M, K) on the
-        host after one stream synchronisation; detections / matches / gradients are in the
-        pinned h_* buffers."""
+    def copy_out(self):
+        """D2H of every result of the step on the current stream; returns the byte count."""
         st = self.step
-        G = gt_host.shape[0]
-        if G > self.max_gt:
-            raise ValueError(f"{G} labels exceed the capacity {self.max_gt}")
-        h2d = 0
-        for d, h in zip(self.d_heads, host_heads):
-            d.copy_(h, non_blocking=True)
-            h2d += h.numel() * 4
-        self.d_gt[:G].copy_(gt_host, non_blocking=True)
-        self.d_off.copy_(off_host, non_blocking=True)
-        h2d += G * 40 + off_host.numel() * 4
-        st.run(self.d_heads, self.d_gt[:G], self.d_off)
         # results: scalars first (small), then the bulk
         self.h_losses.copy_(st.losses4, non_blocking=True)
         self.h_counts[0:1].copy_(st.M, non_blocking=True)
@@ -224,6 +211,107 @@ class HostStep:
             for h, d in zip(self.h_grads, st.grads):
                 h.copy_(d, non_blocking=True)
                 d2h += d.numel() * 4
+        return d2h
+
+    def run(self, host_heads: Sequence[torch.Tensor], gt_host: torch.Tensor, off_host: torch.Tensor):
+        """host_heads / gt_host / off_host: pinned host tensors.  Returns (losses4, M, K) on the
+        host after one stream synchronisation; detections / matches / gradients are in the
+        pinned h_* buffers."""
+        st = self.step
+        G = gt_host.shape[0]
+        if G > self.max_gt:
+            raise ValueError(f"{G} labels exceed the capacity {self.max_gt}")
+        h2d = 0
+        for d, h in zip(self.d_heads, host_heads):
+            d.copy_(h, non_blocking=True)
+            h2d += h.numel() * 4
+        self.d_gt[:G].copy_(gt_host, non_blocking=True)
+        self.d_off.copy_(off_host, non_blocking=True)
+        h2d += G * 40 + off_host.numel() * 4
+        st.run(self.d_heads, self.d_gt[:G], self.d_off)
+        d2h = self.copy_out()
         torch.cuda.current_stream(st.dev).synchronize()
         self.h2d_bytes, self.d2h_bytes = h2d, d2h
         return self.h_losses, int(self.h_counts[0]), int(self.h_counts[1])
+
+
+class HostPipeline:
+    """HostStep with the transfers overlapped: `depth` slots, each with its own device buffers,
+    pinned result buffers and captured step graph; three streams (copy-in, compute, copy-out)
+    chained by events, so that while step i computes, step i+1's heads stream in over PCIe and
+    step i-1's gradients stream out (PCIe is full duplex; the single-stream HostStep serialises
+    the two directions).  Every step still pays its own H2D of the inputs and D2H of all results.
+
+        pipe.submit(host_heads, gt_host, off_host)   -> slot index (enqueues, never blocks unless
+                                                        the slot's previous results are unread)
+        pipe.result(slot)                            -> (losses4, M, K) after that step finished
+    """
+
+    def __init__(self, spec, batch, device, depth=2, with_grad=True, **kw):
+        self.dev, self.depth = device, depth
+        self.slots = [HostStep(spec, batch, device, with_grad=with_grad, **kw) for _ in range(depth)]
+        self.s_in = torch.cuda.Stream(device)
+        self.s_run = torch.cuda.Stream(device)
+        self.s_out = torch.cuda.Stream(device)
+        self.ev_in = [torch.cuda.Event() for _ in range(depth)]
+        self.ev_run = [torch.cuda.Event() for _ in range(depth)]
+        self.ev_out = [torch.cuda.Event() for _ in range(depth)]
+        self.used = [False] * depth
+        self.i = 0
+        self.h2d_bytes = self.d2h_bytes = 0
+        # capture each slot's step graph on its own buffers
+        for hs in self.slots:
+            st = hs.step
+            hs.d_gt.zero_()
+            hs.d_off.zero_()
+            for d in hs.d_heads:
+                d.zero_()
+            with torch.cuda.stream(self.s_run):
+                st.capture(hs.d_heads, hs.d_gt, hs.d_off)
+        torch.cuda.synchronize(device)
+
+    def submit(self, host_heads, gt_host, off_host):
+        k = self.i % self.depth
+        self.i += 1
+        hs = self.slots[k]
+        st = hs.step
+        G = gt_host.shape[0]
+        if G > hs.max_gt:
+            raise ValueError(f"{G} labels exceed the capacity {hs.max_gt}")
+        if self.used[k]:
+            self.ev_out[k].synchronize()  # the slot's previous results must have left the device
+        # copy-in: device input buffers of the slot are free once its previous compute finished
+        with torch.cuda.stream(self.s_in):
+            if self.used[k]:
+                self.s_in.wait_event(self.ev_run[k])
+            h2d = 0
+            for d, h in zip(hs.d_heads, host_heads):
+                d.copy_(h, non_blocking=True)
+                h2d += h.numel() * 4
+            hs.d_gt[:G].copy_(gt_host, non_blocking=True)
+            hs.d_off.copy_(off_host, non_blocking=True)
+            h2d += G * 40 + off_host.numel() * 4
+            self.ev_in[k].record(self.s_in)
+        with torch.cuda.stream(self.s_run):
+            self.s_run.wait_event(self.ev_in[k])
+            if self.used[k]:
+                self.s_run.wait_event(self.ev_out[k])  # results of the previous use were read out
+            st.replay()
+            self.ev_run[k].record(self.s_run)
+        with torch.cuda.stream(self.s_out):
+            self.s_out.wait_event(self.ev_run[k])
+            d2h = hs.copy_out()
+            self.ev_out[k].record(self.s_out)
+        self.used[k] = True
+        self.h2d_bytes, self.d2h_bytes = h2d, d2h
+        return k
+
+    def result(self, k):
+        self.ev_out[k].synchronize()
+        hs = self.slots[k]
+        return hs.h_losses, int(hs.h_counts[0]), int(hs.h_counts[1])
+
+    def drain(self):
+        for k in range(self.depth):
+            if self.used[k]:
+                self.ev_out[k].synchronize()
