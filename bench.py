@@ -201,10 +201,14 @@ def run_native(args):
     # the step as a CUDA graph: 8 kernels on 4 forked/joined streams (pipeline.run_overlapped)
     step.capture(heads, gt_d, off_d)
 
+    # the loss-scalar exchange data-parallel training needs: one 5-float NCCL
+    # all-reduce per step, on its own stream so that it runs under the next step's kernels
+    reducer = ydist.LossAllReduce(dev, B) if world > 1 else None
+
     def one_step():
         step.replay()
-        if world > 1:  # the loss-scalar exchange data-parallel training needs
-            ydist.weighted_mean_losses(step.losses4, B)
+        if reducer is not None:
+            reducer.launch(step.losses4)
 
     for _ in range(W):
         one_step()

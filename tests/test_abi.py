@@ -145,6 +145,9 @@ def _gloo_worker(rank, world, port, q):
     r = oloss.yolo_loss([h[s:e] for h in heads], infos, spec.num_classes, targets[s:e], oloss.LossConfig())
     l4 = torch.stack([r["losses"][k] for k in ("total", "iou", "classification", "objectness")])
     out = ydist.weighted_mean_losses(l4, e - s)
+    red = ydist.LossAllReduce(torch.device("cpu"), e - s)   # the preallocated form bench.py uses
+    red.launch(l4)
+    assert torch.equal(red.result(), out)
     q.put((rank, s, e, l4.tolist(), out.tolist()))
     dist.destroy_process_group()
 

@@ -547,14 +547,35 @@ loss_rows_kernel(const LayerTab t, const GradTab g, const LossParams p,
   // last CTA: fixed-order final sums
   __threadfence();
   __shared__ double s_red[kRowThreads][4];
+  // every thread sums a strided subset; the loads of a thread are independent of its sums,
+  // so they are issued kFinalUnroll at a time (the association is still a fixed one)
+  constexpr int kFinalUnroll = 8;
   double r[4] = {0.0, 0.0, 0.0, 0.0};
-  for (int i = threadIdx.x; i < n_dense_partials; i += kRowThreads)
-    r[3] += __ldcg(&partials[(size_t)i * 4]);
-  for (int i = threadIdx.x; i < (int)gridDim.x; i += kRowThreads) {
-    const double* src = partials + (size_t)(kPartHalf + i) * 4;
-    r[0] += __ldcg(&src[0]);
-    r[1] += __ldcg(&src[1]);
-    r[2] += __ldcg(&src[2]);
+  for (int i0 = threadIdx.x; i0 < n_dense_partials; i0 += kRowThreads * kFinalUnroll) {
+    double v[kFinalUnroll];
+#pragma unroll
+    for (int u = 0; u < kFinalUnroll; ++u) {
+      const int i = i0 + u * kRowThreads;
+      v[u] = (i < n_dense_partials) ? __ldcg(&partials[(size_t)i * 4]) : 0.0;
+    }
+#pragma unroll
+    for (int u = 0; u < kFinalUnroll; ++u) r[3] += v[u];
+  }
+  for (int i0 = threadIdx.x; i0 < (int)gridDim.x; i0 += kRowThreads * kFinalUnroll) {
+    double v[kFinalUnroll][3];
+#pragma unroll
+    for (int u = 0; u < kFinalUnroll; ++u) {
+      const int i = i0 + u * kRowThreads;
+      const double* src = partials + (size_t)(kPartHalf + i) * 4;
+#pragma unroll
+      for (int k = 0; k < 3; ++k) v[u][k] = (i < (int)gridDim.x) ? __ldcg(&src[k]) : 0.0;
+    }
+#pragma unroll
+    for (int u = 0; u < kFinalUnroll; ++u) {
+      r[0] += v[u][0];
+      r[1] += v[u][1];
+      r[2] += v[u][2];
+    }
   }
 #pragma unroll
   for (int k = 0; k < 4; ++k) s_red[threadIdx.x][k] = r[k];
@@ -663,6 +684,8 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
   cudaStream_t s = (cudaStream_t)stream;
   YH_CUDA(cudaSetDevice(ws->device));
   const float numel = (float)((long long)B * tab.N);
+  // 16 CTAs per SM (two waves of 8 resident): measured best on B200 both alone (88 us vs 94 us
+  // at 2..8 CTAs/SM) and inside the overlapped step (profiles/README.md, sweep r1c)
   int dense_grid = ws->num_sms * 16;
   if (dense_grid > kPartHalf) dense_grid = kPartHalf;
   if (!(phases & kPhaseDense)) {
@@ -677,7 +700,7 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
   }
   if (phases & kPhaseDense) YH_LAUNCHED(s);
   if (!(phases & kPhaseRows)) return YH_OK;
-  int row_grid = kPartHalf;  // one warp per matched row where the partial slots allow
+  int row_grid = ws->num_sms * 4;  // resident in one wave; rows beyond that grid-stride
   const int rows_per_cta = (kRowThreads / 32) * kRowsPerWarp;
   const int need = (capacity + rows_per_cta - 1) / rows_per_cta;
   if (row_grid > need) row_grid = need;

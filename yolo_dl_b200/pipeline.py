@@ -121,7 +121,11 @@ class DeviceStep:
         graph (`capture`)."""
         main = torch.cuda.current_stream(self.dev)
         if self._side is None:
-            self._side = [torch.cuda.Stream(self.dev) for _ in range(3)]
+            # decode is bandwidth work (default priority); the assignment and NMS chains are
+            # latency-bound single-CTA-per-image kernels: high priority, so that their few CTAs
+            # are placed as soon as an SM has room
+            self._side = [torch.cuda.Stream(self.dev), torch.cuda.Stream(self.dev, priority=-1),
+                          torch.cuda.Stream(self.dev, priority=-1)]
         s_dec, s_asg, s_nms = self._side
         hp = _lib.ptr_array(heads)
         fork = torch.cuda.Event()
