@@ -199,7 +199,7 @@ def run_native(args):
     step = DeviceStep(spec, B, dev, nms_conf=NMS_CONF, nms_iou=NMS_IOU, by_class=BY_CLASS)
 
     # the step as a CUDA graph: 8 kernels on 4 forked/joined streams (pipeline.run_overlapped)
-    step.capture(heads, gt_d, off_d)
+    step.capture(heads, gt_d, off_d, loss_slots=2 if world > 1 else 1)
 
     # the loss-scalar exchange data-parallel training needs: one 5-float NCCL
     # all-reduce per step, on its own stream so that it runs under the next step's kernels
@@ -208,7 +208,7 @@ def run_native(args):
     def one_step():
         step.replay()
         if reducer is not None:
-            reducer.launch(step.losses4)
+            reducer.launch_weighted(step.weighted5)
 
     for _ in range(W):
         one_step()

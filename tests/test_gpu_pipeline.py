@@ -170,3 +170,25 @@ def test_host_pipeline_overlapped_slots(dev):
         assert torch.equal(g[3], w[3]) and torch.equal(g[4], w[4])
         for x, y in zip(g[5], w[5]):
             assert torch.equal(x, y)
+
+
+def test_capture_with_two_loss_slots_alternates_buffers(dev):
+    spec = synth.small_spec()
+    B = 3
+    heads = [h.to(dev) for h in synth.make_heads(spec, B, 4, obj_mean=-1.0, cls_mean=-1.0)]
+    gt_h, off_h = yh.pack_labels(synth.make_targets(spec, B, 4, n_max=5))
+    gt, off = gt_h.to(dev), off_h.to(dev)
+    step = DeviceStep(spec, B, dev, nms_conf=0.3)
+    step.run(heads, gt, off)
+    torch.cuda.synchronize()
+    want = step.losses4.clone()
+    step.capture(heads, gt, off, loss_slots=2)
+    seen = []
+    for _ in range(4):
+        step.losses4.fill_(float("nan"))
+        step.replay()
+        torch.cuda.synchronize()
+        assert torch.equal(step.losses4, want)
+        seen.append(step.losses4.data_ptr())
+    assert seen[0] == seen[2] and seen[1] == seen[3] and seen[0] != seen[1]
+    assert torch.equal(step.weighted5[:4], want * B) and float(step.weighted5[4]) == B

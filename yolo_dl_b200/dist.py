@@ -52,6 +52,11 @@ class LossAllReduce:
         self.buf = torch.zeros(5, dtype=torch.float32, device=device)
         self.local_batch = float(local_batch)
         self.src[4] = self.local_batch
+        self.launched = False
+        self.n_launched = 0
+        if self.on_cuda:
+            self.ready2 = [torch.cuda.Event(), torch.cuda.Event()]
+            self.done2 = [torch.cuda.Event(), torch.cuda.Event()]
         self.active = dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
         if self.on_cuda:
             self.stream = torch.cuda.Stream(device)
@@ -62,13 +67,19 @@ class LossAllReduce:
         torch.mul(losses4.detach(), self.local_batch, out=self.src[:4])
         self.buf.copy_(self.src)
 
-    def launch(self, losses4: torch.Tensor):
+    def launch(self, losses4: torch.Tensor, wait_taken: bool = True):
+        """`wait_taken=False`: the caller guarantees that `losses4` is not overwritten before
+        the NEXT launch (DeviceStep.capture(loss_slots=2) alternates two buffers), so the
+        producing stream is not made to wait for this launch's read — only for the previous one."""
         if not self.on_cuda:
             self._enqueue(losses4)
             if self.active:
                 dist.all_reduce(self.buf, op=dist.ReduceOp.SUM, group=self.group)
             return
         cur = torch.cuda.current_stream(losses4.device)
+        if not wait_taken and self.launched:
+            cur.wait_event(self.taken)  # the previous launch has read its buffer
+        self.launched = True
         ready = torch.cuda.Event()
         ready.record(cur)
         with torch.cuda.stream(self.stream):
@@ -78,9 +89,29 @@ class LossAllReduce:
             if self.active:
                 dist.all_reduce(self.buf, op=dist.ReduceOp.SUM, group=self.group)
             self.done.record(self.stream)
-        cur.wait_event(self.taken)  # losses4 may be overwritten by the next step from here on
+        if wait_taken:
+            cur.wait_event(self.taken)  # losses4 may be overwritten by the next step from here on
 
     def result(self) -> torch.Tensor:
         if self.on_cuda:
             self.done.synchronize()
         return self.buf[:4] / self.buf[4]
+
+    def launch_weighted(self, weighted5: torch.Tensor):
+        """`weighted5` = [loss*B_local (4), B_local] already on the device (DeviceStep.weighted5,
+        written inside the step graph into one of two alternating buffers): the all-reduce runs in
+        place on it, on this object's stream; nothing else is launched and the producing stream
+        never waits for it (only for the launch before the previous one)."""
+        cur = torch.cuda.current_stream(weighted5.device)
+        k = self.n_launched & 1
+        self.n_launched += 1
+        if self.n_launched > 2:
+            cur.wait_event(self.done2[k])  # same buffer, two launches ago: finished long since
+        self.ready2[k].record(cur)
+        self.stream.wait_event(self.ready2[k])
+        if self.active:
+            with torch.cuda.stream(self.stream):
+                dist.all_reduce(weighted5, op=dist.ReduceOp.SUM, group=self.group)
+        self.done2[k].record(self.stream)
+        self.buf = weighted5
+        self.done = self.done2[k]

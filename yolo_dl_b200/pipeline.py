@@ -147,23 +147,48 @@ class DeviceStep:
         main.wait_event(joins[0])
         main.wait_event(joins[2])
 
-    def capture(self, heads, gt_dev, off_dev):
+    def capture(self, heads, gt_dev, off_dev, loss_slots: int = 1):
         """Captures `run_overlapped` on these buffers into a CUDA graph; `replay()` launches it.
-        The captured pointers are those of `heads`/`gt_dev`/`off_dev`: refill them in place."""
+        The captured pointers are those of `heads`/`gt_dev`/`off_dev`: refill them in place.
+        `loss_slots` > 1 captures that many copies of the graph that differ only in the
+        `losses4` buffer they write and replays them round-robin, so that a consumer on another
+        stream (the data-parallel loss all-reduce, dist.LossAllReduce) can still read step i's
+        scalars while step i+1 runs."""
         self._keep = (list(heads), gt_dev, off_dev)
         self.run_overlapped(heads, gt_dev, off_dev)  # warm: module attributes, streams
         torch.cuda.synchronize(self.dev)
-        g = torch.cuda.CUDAGraph()
+        # [total, iou, cls, obj, 1] per slot; `weighted5` = that times the local batch size, the
+        # operand of the data-parallel weighted mean (multi_gpu.rs:188-195), produced in-graph
+        self._l5_ring = [torch.zeros(5, dtype=torch.float32, device=self.dev) for _ in range(loss_slots)]
+        self._w5_ring = [torch.zeros(5, dtype=torch.float32, device=self.dev) for _ in range(loss_slots)]
+        for l5 in self._l5_ring:
+            l5[4] = 1.0
+        self._loss_ring = [l5[:4] for l5 in self._l5_ring]
+        self._graphs = []
         cap = torch.cuda.Stream(self.dev)
-        before = int(self.lib.yh_launch_count(0))
-        with torch.cuda.graph(g, stream=cap):
-            self.run_overlapped(heads, gt_dev, off_dev)
-        self.kernels_in_graph = int(self.lib.yh_launch_count(0)) - before
-        self._graph = g
-        return g
+        for k in range(loss_slots):
+            self.losses4 = self._loss_ring[k]
+            g = torch.cuda.CUDAGraph()
+            before = int(self.lib.yh_launch_count(0))
+            with torch.cuda.graph(g, stream=cap):
+                self.run_overlapped(heads, gt_dev, off_dev)
+                if loss_slots > 1:
+                    torch.mul(self._l5_ring[k], float(self.B), out=self._w5_ring[k])
+            self.kernels_in_graph = int(self.lib.yh_launch_count(0)) - before
+            self._graphs.append(g)
+        self._replays = 0
+        self._graph = self._graphs[0]
+        self.losses4 = self._loss_ring[0]
+        self.weighted5 = self._w5_ring[0]
+        return self._graph
 
     def replay(self):
-        self._graph.replay()
+        """Launches the captured step; afterwards `self.losses4` is the buffer this replay writes."""
+        k = self._replays % len(self._graphs)
+        self._replays += 1
+        self.losses4 = self._loss_ring[k]
+        self.weighted5 = self._w5_ring[k]
+        self._graphs[k].replay()
 
     def counts(self):
         """synchronising read of (M, K); raises on overflow."""
