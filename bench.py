@@ -249,9 +249,10 @@ def run_native(args):
     reps = max(5, min(K, 20))
     for _ in range(reps):
         step.run(heads, gt_d, off_d)
-    sums = (ctypes.c_double * 10)()
-    cnts = (ctypes.c_int64 * 10)()
-    _lib.check(lib.yh_timing_read(sums, cnts, 10))
+    nk = len(_lib.KERNEL_NAMES)
+    sums = (ctypes.c_double * nk)()
+    cnts = (ctypes.c_int64 * nk)()
+    _lib.check(lib.yh_timing_read(sums, cnts, nk))
     lib.yh_timing_enable(0)
     kern_ms = {n: sums[i] / cnts[i] for i, n in enumerate(_lib.KERNEL_NAMES) if cnts[i]}
     alg = step.algorithmic_bytes()

@@ -193,6 +193,18 @@ int yh_nms_by_scores(YhWorkspace* ws, const float* ltrb, const float* scores,
                      const int64_t* groups, int K, double iou_threshold, int64_t* keep,
                      int32_t* out_K_dev, void* stream);
 
+/* ---- f2: the counters of YoloBenchmark::forward (`yolo-dl/src/loss/benchmark.rs:34-100`).
+ * One launch; counts5_dev (device int64[5]) receives
+ *   [all_count = B*N, all_pos = #{sigmoid(obj) >= thr}, matched_count = M,
+ *    matched_pos = #{sigmoid(obj of matched rows) >= thr},
+ *    class_hits = #{any_c(conf_c >= thr) && argmax_c(class logit) == target class}]
+ * from which the caller forms obj_accuracy / obj_recall / obj_precision / class_accuracy in f64
+ * exactly as benchmark.rs:59-92.  pred_rows_dev / m_class / M_dev are the outputs of
+ * yh_loss_fwd_bwd and yh_assign.  The threshold is compared in f32 like `Tensor::ge(f64)`. */
+int yh_benchmark(YhWorkspace* ws, const float* const* heads, const YhLayer* layers, int L, int B,
+                 int C, const float* pred_rows_dev, const int64_t* m_class, const int32_t* M_dev,
+                 int capacity, double confidence_threshold, int64_t* counts5_dev, void* stream);
+
 /* ---- a14: YoloInference::forward post-pass (`yolo-dl/src/loss/inference.rs:50-77`):
  * among kept rows of the same (batch, instance) keep the one with max confidence.
  * max_by_key keeps the LAST maximum: equal confidences keep the later row.
@@ -212,9 +224,9 @@ int64_t yh_launch_count(int reset);
 /* Optional per-launch timing for benchmarks: while enabled (thread-local) every kernel launch of
  * this library is bracketed by a CUDA event pair on its launch stream.  yh_timing_read
  * synchronises on those events and returns, per kernel id (order: decode, assign_slots,
- * assign_emit, loss_dense, loss_rows, nms_filter, nms_segment, nms_emit, nms_pack, pick), the
- * summed device time in ms and the launch count since the last read. */
-#define YH_NUM_KERNELS 10
+ * assign_emit, loss_dense, loss_rows, nms_filter, nms_segment, nms_emit, nms_pack, pick,
+ * benchmark), the summed device time in ms and the launch count since the last read. */
+#define YH_NUM_KERNELS 11
 int yh_timing_enable(int on);
 int yh_timing_read(double* ms_sum, int64_t* launches, int n);
 

@@ -171,3 +171,13 @@ def test_loss_scalar_all_reduce_gloo_world2():
     expect = (np.array(l0) * 3 + np.array(l1) * 2) / 5
     np.testing.assert_allclose(o0, expect, rtol=1e-6)
     np.testing.assert_allclose(o1, expect, rtol=1e-6)
+
+
+def test_benchmark_ratios_follow_reference_expressions():
+    """benchmark.rs:47-92 on integer counts (the host half of YoloBenchmark)."""
+    from yolo_dl_b200.benchmark import ratios_from_counts
+    r = ratios_from_counts(1000, 40, 20, 10, 5)
+    assert r.obj_accuracy == (10 + (960 - 10)) / 1000 and r.obj_recall == 0.5
+    assert r.obj_precision == 0.25 and r.class_accuracy == 0.25
+    r = ratios_from_counts(1000, 0, 0, 0, 0)
+    assert r.obj_recall == 1.0 and r.obj_precision == 1.0 and r.class_accuracy == 1.0

@@ -1,0 +1,60 @@
+"""yh_benchmark (YoloBenchmark::forward, benchmark.rs:34-100) against the oracle restatement."""
+import pytest
+import torch
+
+import yolo_dl_b200 as yh
+from oracle import benchmark as obench, detect as odet, loss as oloss
+from yolo_dl_b200 import synth
+from util import build
+
+pytestmark = pytest.mark.gpu
+
+
+def run_case(dev, spec, B, seed, thr, obj_mean, cls_mean, n_max):
+    heads_cpu = synth.make_heads(spec, B, seed, obj_mean=obj_mean, cls_mean=cls_mean)
+    targets = synth.make_targets(spec, B, seed, n_max=n_max)
+    heads, detects, merged, infos = build(spec, heads_cpu, dev)
+    loss = yh.YoloLossInit(box_metric="ciou").build()
+    with torch.no_grad():
+        out, aux = loss.forward(merged, targets)
+    bench = yh.YoloBenchmarkInit(iou_threshold=0.5, confidence_threshold=thr).build()
+    got_counts = bench.counts(merged, aux.matchings).tolist()
+    got = bench.forward(merged, aux.matchings, None)
+
+    ref = oloss.yolo_loss(heads_cpu, infos, spec.num_classes, targets, oloss.LossConfig(box_metric="ciou"),
+                          want_grad=False)
+    om = odet.forward_merged(heads_cpu, infos, spec.num_classes)
+    want, want_counts = obench.yolo_benchmark(om, ref["pred"], torch.from_numpy(ref["matches"][4]), thr)
+    assert got_counts == want_counts
+    assert got.obj_accuracy == want["obj_accuracy"] and got.obj_recall == want["obj_recall"]
+    assert got.obj_precision == want["obj_precision"] and got.class_accuracy == want["class_accuracy"]
+    return got_counts
+
+
+@pytest.mark.parametrize("thr", [0.1, 0.5])
+def test_benchmark_small(dev, thr):
+    c = run_case(dev, synth.small_spec(), 4, 11, thr, -0.5, 0.0, 6)
+    assert c[1] > 0 and c[3] >= 0 and c[2] > 0
+
+
+def test_benchmark_yolov4_608(dev):
+    c = run_case(dev, synth.yolov4_608(), 8, 12, 0.4, -3.0, -1.0, 30)
+    assert c[0] == 8 * 22743 and c[1] > 0
+
+
+def test_benchmark_tiny_416_many_images(dev):
+    run_case(dev, synth.yolov4_tiny_416(), 32, 13, 0.25, -2.0, -0.5, 10)
+
+
+def test_benchmark_no_matches(dev):
+    spec = synth.small_spec()
+    heads_cpu = synth.make_heads(spec, 2, 5, obj_mean=-1.0, cls_mean=-1.0)
+    heads, detects, merged, infos = build(spec, heads_cpu, dev)
+    loss = yh.YoloLossInit().build()
+    with torch.no_grad():
+        out, aux = loss.forward(merged, [[], []])
+    got = yh.YoloBenchmarkInit(0.5, 0.3).build().forward(merged, aux.matchings, None)
+    assert got.obj_recall == 1.0 and got.class_accuracy == 1.0  # benchmark.rs:62-66,92-94
+    om = odet.forward_merged(heads_cpu, infos, spec.num_classes)
+    all_pos = int(om["obj_logit"].sigmoid().ge(0.3).count_nonzero())
+    assert got.obj_precision == (0.0 if all_pos else 1.0)

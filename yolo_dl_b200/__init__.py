@@ -7,6 +7,7 @@ CPU fallback and never imports `oracle/`.
 """
 from . import _lib
 from ._lib import YoloHotError, load
+from .benchmark import YoloBenchmark, YoloBenchmarkInit, YoloBenchmarkOutput
 from .detect import Detect2D, Detect2DInit, MergeDetect2D, MergedDenseDetection
 from .loss import CyCxHWMatcher, CyCxHWMatcherInit, YoloLoss, YoloLossInit, pack_labels
 from .nms import (NonMaxSuppression, NonMaxSuppressionInit, YoloInference, YoloInferenceInit,

@@ -68,6 +68,8 @@ SYMBOLS = {
                                  c_void_p, c_void_p]),
     "yh_inference_pick": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                   c_void_p, c_int, c_void_p]),
+    "yh_benchmark": (c_int, [c_void_p, _PF, POINTER(YhLayer), c_int, c_int, c_int, c_void_p, c_void_p,
+                             c_void_p, c_int, c_double, c_void_p, c_void_p]),
     "yh_read_counts": (c_int, [c_void_p, c_void_p, POINTER(c_int32), c_void_p, POINTER(c_int32),
                                c_void_p]),
     "yh_launch_count": (c_int64, [c_int]),
@@ -77,7 +79,7 @@ SYMBOLS = {
 
 KERNEL_NAMES = ["decode_kernel", "assign_slots_kernel", "assign_emit_kernel", "loss_dense_kernel",
                 "loss_rows_kernel", "nms_filter_kernel", "nms_segment_kernel", "nms_emit_kernel",
-                "nms_pack_kernel", "pick_kernel"]
+                "nms_pack_kernel", "pick_kernel", "benchmark_kernel"]
 
 _lib = None
 

@@ -125,7 +125,7 @@ def _matching_output(prediction, a: _Assigned, M: int, pred_rows) -> MatchingOut
                               pr[:, 4:5], pr[:, 5:]),
         LabelTensor(CyCxHWTensor(tg[:, 0:1], tg[:, 1:2], tg[:, 2:3], tg[:, 3:4]),
                     a.cls[:M].view(-1, 1)),
-        a.gt[:M])
+        a.gt[:M], pr)
 
 
 @dataclass

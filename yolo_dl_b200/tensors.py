@@ -151,6 +151,7 @@ class MatchingOutput:
     pred: ObjectDetectionTensor
     target: LabelTensor
     gt_rows: torch.Tensor = None  # [M] i32: row of the packed GT list that won the slot
+    pred_rows: torch.Tensor = None  # [M, 5+C] contiguous rows `pred` is a view of (yh_benchmark input)
 
     def num_samples(self):
         return self.pred_indexes.num_samples()
