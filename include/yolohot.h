@@ -205,6 +205,36 @@ int yh_benchmark(YhWorkspace* ws, const float* const* heads, const YhLayer* laye
                  int C, const float* pred_rows_dev, const int64_t* m_class, const int32_t* M_dev,
                  int capacity, double confidence_threshold, int64_t* counts5_dev, void* stream);
 
+/* ---- f4: evaluation metrics, f64 like the reference's R64 host code.
+ * yh_match_det_gt = match_det_gt (`yolo-dl/src/loss/pred_gt_matching.rs:109-142`) with the scalar
+ * `bbox::RectFloat::iou_with(.., 1e-8)` (`bbox/src/rect.rs:113-140`), batched over S segments
+ * (an image, or an image x class: the caller's grouping).  Boxes are f64 (t,l,b,r) rows;
+ * det_offsets_dev / gt_offsets_dev are [S+1] int32 prefix offsets.  Per detection:
+ *   out_gt_dev   row (into gts) of the ground truth of maximum IoU among ALL ground truths of its
+ *                segment — the LAST of equal maxima (Iterator::max_by_key) — or -1 when that IoU
+ *                is 0 within f64 epsilon (:131) or the segment has no ground truth (the
+ *                reference would panic on the empty max, :128);
+ *   out_iou_dev  `DetBoxStruct::iou` (:96-106): IoU with that ground truth, 0 for none. */
+int yh_match_det_gt(const double* dets_tlbr_dev, const int32_t* det_offsets_dev, int D,
+                    const double* gts_tlbr_dev, const int32_t* gt_offsets_dev, int S,
+                    int32_t* out_gt_dev, double* out_iou_dev, void* stream);
+
+/* yh_average_precision = ApCalculator::compute_by_detections for every (problem, IoU threshold)
+ * (`yolo-dl/src/loss/average_precision.rs:157-219`, envelope + n-point interpolation :87-155,
+ * `utils/algorithm.rs:38-91`).  A problem is a contiguous range of detections
+ * [problem_offsets[p], problem_offsets[p+1]) (typically one class) with num_ground_truth[p];
+ * det_gt / det_iou / det_conf are yh_match_det_gt's outputs and the detections' confidences.
+ * out_ap_dev is [num_problems, num_thresholds] f64; MeanApCalculator::compute_mean_ap (:252-275)
+ * is the mean of a row.  Detections of equal confidence are ordered by (ground truth ascending,
+ * none first; IoU descending; index) — the reference iterates a HashMap there (unspecified).
+ * max_detections_per_problem <= 8192; n_points in 2..1024 (COCO: 101).  An empty problem yields 0
+ * (the reference panics, :90). */
+int yh_average_precision(const int32_t* det_gt_dev, const double* det_iou_dev,
+                         const double* det_conf_dev, const int32_t* problem_offsets_dev,
+                         const int32_t* num_ground_truth_dev, int num_problems,
+                         int max_detections_per_problem, const double* iou_thresholds_dev,
+                         int num_thresholds, int n_points, double* out_ap_dev, void* stream);
+
 /* ---- a14: YoloInference::forward post-pass (`yolo-dl/src/loss/inference.rs:50-77`):
  * among kept rows of the same (batch, instance) keep the one with max confidence.
  * max_by_key keeps the LAST maximum: equal confidences keep the later row.
@@ -225,8 +255,9 @@ int64_t yh_launch_count(int reset);
  * this library is bracketed by a CUDA event pair on its launch stream.  yh_timing_read
  * synchronises on those events and returns, per kernel id (order: decode, assign_slots,
  * assign_emit, loss_dense, loss_rows, nms_filter, nms_segment, nms_emit, nms_pack, pick,
- * benchmark), the summed device time in ms and the launch count since the last read. */
-#define YH_NUM_KERNELS 11
+ * benchmark, match_det_gt, ap), the summed device time in ms and the launch count since the last
+ * read. */
+#define YH_NUM_KERNELS 13
 int yh_timing_enable(int on);
 int yh_timing_read(double* ms_sum, int64_t* launches, int n);
 

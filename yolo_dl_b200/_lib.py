@@ -70,6 +70,10 @@ SYMBOLS = {
                                   c_void_p, c_int, c_void_p]),
     "yh_benchmark": (c_int, [c_void_p, _PF, POINTER(YhLayer), c_int, c_int, c_int, c_void_p, c_void_p,
                              c_void_p, c_int, c_double, c_void_p, c_void_p]),
+    "yh_match_det_gt": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p, c_void_p,
+                                c_void_p]),
+    "yh_average_precision": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
+                                     c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "yh_read_counts": (c_int, [c_void_p, c_void_p, POINTER(c_int32), c_void_p, POINTER(c_int32),
                                c_void_p]),
     "yh_launch_count": (c_int64, [c_int]),
@@ -79,7 +83,8 @@ SYMBOLS = {
 
 KERNEL_NAMES = ["decode_kernel", "assign_slots_kernel", "assign_emit_kernel", "loss_dense_kernel",
                 "loss_rows_kernel", "nms_filter_kernel", "nms_segment_kernel", "nms_emit_kernel",
-                "nms_pack_kernel", "pick_kernel", "benchmark_kernel"]
+                "nms_pack_kernel", "pick_kernel", "benchmark_kernel",
+                "match_det_gt_kernel", "ap_kernel"]
 
 _lib = None
 

@@ -144,3 +144,215 @@ __device__ void bitonic_sort_idx(int* s, const int P, const Less less) {
     }
   }
 }
+
+// block-wide inclusive scans over `n` ints / doubles in shared memory, chunked: thread t owns the
+// contiguous elements [t*per, (t+1)*per); s_part[kApThreads] is scratch
+__device__ void block_inclusive_sum(int* a, const int n, int* s_part) {
+  const int per = (n + kApThreads - 1) / kApThreads;
+  const int lo = threadIdx.x * per, hi = min(n, lo + per);
+  int run = 0;
+  for (int i = lo; i < hi; ++i) {
+    run += a[i];
+    a[i] = run;
+  }
+  s_part[threadIdx.x] = run;
+  __syncthreads();
+  // Hillis-Steele over the kApThreads partial sums
+  for (int o = 1; o < kApThreads; o <<= 1) {
+    const int v = (threadIdx.x >= o) ? s_part[threadIdx.x - o] : 0;
+    __syncthreads();
+    s_part[threadIdx.x] += v;
+    __syncthreads();
+  }
+  const int before = threadIdx.x ? s_part[threadIdx.x - 1] : 0;
+  for (int i = lo; i < hi; ++i) a[i] += before;
+  __syncthreads();
+}
+
+// suffix maximum in place: a[i] = max(a[i..n))
+__device__ void block_suffix_max(double* a, const int n, double* s_part) {
+  const int per = (n + kApThreads - 1) / kApThreads;
+  const int lo = threadIdx.x * per, hi = min(n, lo + per);
+  double run = -INFINITY;
+  for (int i = hi - 1; i >= lo; --i) {
+    run = fmax(run, a[i]);
+    a[i] = run;
+  }
+  s_part[threadIdx.x] = run;
+  __syncthreads();
+  for (int o = 1; o < kApThreads; o <<= 1) {
+    const double v = (threadIdx.x + o < kApThreads) ? s_part[threadIdx.x + o] : -INFINITY;
+    __syncthreads();
+    s_part[threadIdx.x] = fmax(s_part[threadIdx.x], v);
+    __syncthreads();
+  }
+  const double after = (threadIdx.x + 1 < kApThreads) ? s_part[threadIdx.x + 1] : -INFINITY;
+  for (int i = lo; i < hi; ++i) a[i] = fmax(a[i], after);
+  __syncthreads();
+}
+
+// dynamic shared memory layout (P = next pow2 of D, D <= kApMax):
+//   int    idx[P]      sorted detection indices (order 2)
+//   int    tp[P]       per position: is TP -> running TP
+//   double env[P]      per position: precision -> suffix max
+//   u8     best[P]     detection (by LOCAL index) is the best of its ground truth
+//   scratch for the scans / the point values
+__global__ void __launch_bounds__(kApThreads)
+ap_kernel(const int* __restrict__ det_gt, const double* __restrict__ det_iou,
+          const double* __restrict__ det_conf, const int* __restrict__ prob_off,
+          const int* __restrict__ num_gt, const double* __restrict__ thresholds, const int T,
+          const int n_points, double* __restrict__ out_ap) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const int p = blockIdx.x;
+  const int d0 = prob_off[p], D = prob_off[p + 1] - d0;
+  if (D <= 0) {  // the reference panics on an empty curve (average_precision.rs:90); 0 here
+    for (int k = threadIdx.x; k < T; k += kApThreads) out_ap[(size_t)p * T + k] = 0.0;
+    return;
+  }
+  int P = 2;
+  while (P < D) P <<= 1;
+  double* env = reinterpret_cast<double*>(smem);
+  double* s_dpart = env + P;                       // kApThreads doubles (also the point values)
+  int* idx = reinterpret_cast<int*>(s_dpart + kApThreads);
+  int* tp = idx + P;
+  int* s_ipart = tp + P;                           // kApThreads ints
+  unsigned char* best = reinterpret_cast<unsigned char*>(s_ipart + kApThreads);
+
+  ApView v;
+  v.gt = det_gt + d0;
+  v.iou = det_iou + d0;
+  v.conf = det_conf + d0;
+
+  // order 1 -> best-of-ground-truth flags (:171-189)
+  for (int i = threadIdx.x; i < P; i += kApThreads) idx[i] = i < D ? i : 0x7fffffff;
+  __syncthreads();
+  bitonic_sort_idx(idx, P, ByGroup{v});
+  for (int i = threadIdx.x; i < D; i += kApThreads) {
+    const int me = idx[i];
+    best[me] = (i == 0 || v.gt[idx[i - 1]] != v.gt[me]) ? 1 : 0;
+  }
+  __syncthreads();
+  // order 2 (:194); the list is already in order 1, any correct sort gives the same result
+  bitonic_sort_idx(idx, P, ByConf{v});
+
+  const double ngt = (double)num_gt[p];
+  for (int k = 0; k < T; ++k) {
+    const double thr = thresholds[k];
+    for (int i = threadIdx.x; i < D; i += kApThreads) {
+      const int me = idx[i];
+      tp[i] = (best[me] && v.iou[me] >= thr) ? 1 : 0;
+    }
+    __syncthreads();
+    block_inclusive_sum(tp, D, s_ipart);
+    // precision = tp / (tp + fp), tp + fp = position + 1  (:199-213)
+    for (int i = threadIdx.x; i < D; i += kApThreads) {
+      const double a = (double)tp[i], b = (double)(i + 1 - tp[i]);
+      env[i] = a / (a + b);
+    }
+    __syncthreads();
+    block_suffix_max(env, D, s_dpart);  // precision envelope (:102-135)
+
+    // sentinel `last` (:97-100): recall min(max_recall + 1e-3, 1), precision 0
+    const double max_recall = (double)tp[D - 1] / ngt;
+    const double r_last = fmin(max_recall + 1e-3, 1.0);
+    // interpolation points (:141-149, algorithm.rs:38-91): the value at x is the envelope at the
+    // first curve entry with recall > x; past the last entry only the point that exhausts the
+    // curve may contribute (its precision if that recall is exactly 1)
+    double val = 0.0;
+    if ((int)threadIdx.x < n_points) {
+      const double x = (double)threadIdx.x / (double)(n_points - 1);
+      // entries j = 0..D-1 real (recall tp[j]/ngt), j = D the sentinel
+      int lo = 0, hi = D + 1;  // first j with recall_j > x, D+1 = none
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        const double r = mid < D ? (double)tp[mid] / ngt : r_last;
+        if (r > x) hi = mid; else lo = mid + 1;
+      }
+      if (lo <= D) {
+        val = lo < D ? env[lo] : 0.0;
+      } else {
+        // x >= r_last: this point contributes only if it is the FIRST such point and r_last == 1
+        const bool first_past = threadIdx.x == 0 ||
+                                !((double)(threadIdx.x - 1) / (double)(n_points - 1) >= r_last);
+        if (first_past && r_last == 1.0) {
+          int a = 0, b = D;  // first j with recall_j >= 1.0 (sentinel at D qualifies)
+          while (a < b) {
+            const int mid = (a + b) >> 1;
+            if ((double)tp[mid] / ngt >= 1.0) b = mid; else a = mid + 1;
+          }
+          val = a < D ? env[a] : 0.0;
+        }
+      }
+    }
+    __syncthreads();
+    if ((int)threadIdx.x < n_points) s_dpart[threadIdx.x] = val;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double s = 0.0;
+      for (int i = 0; i < n_points; ++i) s += s_dpart[i];  // Iterator::sum order (:148)
+      out_ap[(size_t)p * T + k] = s / (double)n_points;
+    }
+    __syncthreads();
+  }
+}
+
+static size_t ap_smem_bytes(int P) {
+  return (size_t)P * sizeof(double) + kApThreads * sizeof(double) + 2 * (size_t)P * sizeof(int) +
+         kApThreads * sizeof(int) + (size_t)P;
+}
+
+}  // namespace yh
+
+extern "C" {
+
+int yh_match_det_gt(const double* dets_tlbr_dev, const int32_t* det_offsets_dev, int D,
+                    const double* gts_tlbr_dev, const int32_t* gt_offsets_dev, int S,
+                    int32_t* out_gt_dev, double* out_iou_dev, void* stream) {
+  using namespace yh;
+  YH_REQUIRE(D >= 0 && S >= 1, "D=%d S=%d", D, S);
+  YH_REQUIRE(det_offsets_dev && gt_offsets_dev, "offsets are NULL");
+  if (D == 0) return YH_OK;
+  // gts may be NULL when no segment has a ground truth (it is then never dereferenced)
+  YH_REQUIRE(dets_tlbr_dev && out_gt_dev && out_iou_dev, "NULL argument");
+  YH_REQUIRE((((uintptr_t)dets_tlbr_dev | (uintptr_t)gts_tlbr_dev) & 31) == 0,
+             "boxes must be 32-byte aligned");
+  cudaStream_t s = (cudaStream_t)stream;
+  const int warps = kMatchThreads / 32;
+  YH_TIME(YH_K_MATCH_DET_GT, s);
+  match_det_gt_kernel<<<(D + warps - 1) / warps, kMatchThreads, 0, s>>>(
+      dets_tlbr_dev, det_offsets_dev, gts_tlbr_dev, gt_offsets_dev, S, D, 1e-8, out_gt_dev,
+      out_iou_dev);
+  YH_LAUNCHED(s);
+  return YH_OK;
+}
+
+int yh_average_precision(const int32_t* det_gt_dev, const double* det_iou_dev,
+                         const double* det_conf_dev, const int32_t* problem_offsets_dev,
+                         const int32_t* num_ground_truth_dev, int num_problems,
+                         int max_detections_per_problem, const double* iou_thresholds_dev,
+                         int num_thresholds, int n_points, double* out_ap_dev, void* stream) {
+  using namespace yh;
+  YH_REQUIRE(num_problems >= 1 && num_thresholds >= 1, "num_problems=%d num_thresholds=%d",
+             num_problems, num_thresholds);
+  // ApCalculator::new (:72-84); a single point divides by n_points-1 = 0 in the reference
+  YH_REQUIRE(n_points >= 2 && n_points <= kApThreads, "invalid number of interpolated points %d",
+             n_points);
+  YH_REQUIRE(max_detections_per_problem >= 0 && max_detections_per_problem <= kApMax,
+             "%d detections in one problem > %d", max_detections_per_problem, kApMax);
+  YH_REQUIRE(problem_offsets_dev && num_ground_truth_dev && iou_thresholds_dev && out_ap_dev,
+             "NULL argument");
+  int P = 2;
+  while (P < max_detections_per_problem) P <<= 1;
+  const size_t smem = ap_smem_bytes(P);
+  cudaStream_t s = (cudaStream_t)stream;
+  YH_CUDA(cudaFuncSetAttribute(ap_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  YH_TIME(YH_K_AP, s);
+  ap_kernel<<<num_problems, kApThreads, smem, s>>>(det_gt_dev, det_iou_dev, det_conf_dev,
+                                                   problem_offsets_dev, num_ground_truth_dev,
+                                                   iou_thresholds_dev, num_thresholds, n_points,
+                                                   out_ap_dev);
+  YH_LAUNCHED(s);
+  return YH_OK;
+}
+
+}  // extern "C"
