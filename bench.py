@@ -12,7 +12,7 @@ the 126 MB L2, so every step streams from HBM) and 1..30 GT boxes per image; CIo
 reference's default weights, Rect4 matching, NMS at the shipped thresholds (conf .4 / IoU .5,
 train.json5:153-154) per class.  Weak scaling: every rank owns its own 64 images; the only
 collective is the 5-float loss all-reduce.  One step = yh_decode_merged + yh_assign +
-yh_loss_dense + yh_loss_rows (with the full head gradient) + yh_nms = 8 kernels, captured once as
+yh_loss_dense + yh_loss_rows_compute + yh_loss_finish (full head gradient) + yh_nms = 9 kernels, captured once as
 a CUDA graph over four forked/joined streams (yolo_dl_b200/pipeline.py) and replayed per step.
 """
 import argparse
@@ -198,7 +198,7 @@ def run_native(args):
     gt_d, off_d = gt_h.to(dev), off_h.to(dev)
     step = DeviceStep(spec, B, dev, nms_conf=NMS_CONF, nms_iou=NMS_IOU, by_class=BY_CLASS)
 
-    # the step as a CUDA graph: 8 kernels on 4 forked/joined streams (pipeline.run_overlapped)
+    # the step as a CUDA graph: 9 kernels on 4 forked/joined streams (pipeline.run_overlapped)
     step.capture(heads, gt_d, off_d, loss_slots=2 if world > 1 else 1)
 
     # the loss-scalar exchange data-parallel training needs: one 5-float NCCL
@@ -230,7 +230,7 @@ def run_native(args):
         ms = float(t)
     value = world * B * K / (ms * 1e-3)
 
-    # the same 8 kernels launched one after another on one stream (no graph), for comparison
+    # the same 9 kernels launched one after another on one stream (no graph), for comparison
     Ks = max(3, min(K, 50))
     for _ in range(3):
         step.run(heads, gt_d, off_d)
@@ -334,7 +334,7 @@ def run_native(args):
         hl, hM, hK = last["r"]
         e2e = {"value": world * B * Ke / (ems * 1e-3), "unit": UNIT, "h2d_bytes_per_step": pipe.h2d_bytes,
                "d2h_bytes_per_step": pipe.d2h_bytes, "steps": Ke, "ms_per_step": ems / Ke,
-               "includes": "per step: H2D heads+labels, 8 kernels (graph), D2H losses+matches+detections+head "
+               "includes": "per step: H2D heads+labels, 9 kernels (graph), D2H losses+matches+detections+head "
                            "gradients; 2-slot pipeline over copy-in/compute/copy-out streams; timed by "
                            "max(wall clock, CUDA events) around the loop incl. the final drain",
                "unpipelined_ms_per_step": serial_ms / Ke,
@@ -354,7 +354,7 @@ def run_native(args):
                 "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f32", "data": "synthetic", "config": workload_config(args, world),
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches,
-                "execution": "CUDA graph of 8 kernels on 4 forked/joined streams, replayed once per step",
+                "execution": "CUDA graph of 9 kernels on 4 forked/joined streams, replayed once per step",
                 "sequential_ms_per_step": seq_ms,
                 "clocks": clk.summary(), "matches_per_step": M, "detections_per_step": Kdet,
                 "loss": float(step.losses4[0])}

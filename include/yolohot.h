@@ -96,6 +96,10 @@ typedef struct YhWorkspace YhWorkspace;
 int yh_workspace_create(int device, int max_batch, int64_t max_instances,
                         int cand_per_image, YhWorkspace** out);
 int yh_workspace_destroy(YhWorkspace* ws);
+/* Reserves the staging buffer of the matched-row gradients ([capacity, 5+C] f32) that the loss
+ * phases use.  The loss calls grow it on demand, but not while their stream is being captured
+ * into a CUDA graph (no allocation inside a capture): a capturing caller reserves first. */
+int yh_workspace_reserve_rows(YhWorkspace* ws, int capacity, int C);
 const char* yh_last_error(void);
 const char* yh_version(void);
 
@@ -148,15 +152,21 @@ int yh_loss_fwd_bwd(YhWorkspace* ws, const float* const* heads, const YhLayer* l
                     float* iou_score_dev, float* pred_rows_dev, float* const* grad_heads,
                     void* stream);
 
-/* The two phases of yh_loss_fwd_bwd as separate calls, so that a caller with streams can overlap
+/* The phases of yh_loss_fwd_bwd as separate calls, so that a caller with streams can overlap
  * them with the rest of the step (YoloLoss::forward does assign -> loss strictly in sequence,
  * `loss_.rs:233-256`, although the dense objectness pass needs no matches):
- *   yh_loss_dense  the objectness BCE over all B*N cells against target 0 and, if grad_heads, the
- *                  whole head gradient (zeros + sigmoid(x)*w/(B*N)).  Needs only the heads: may
- *                  run concurrently with yh_assign / yh_decode / yh_nms on other streams.
- *   yh_loss_rows   the M matched rows (box metric, class BCE, objectness correction, their
- *                  gradients) and the final reduction into losses4_dev.  Must be ordered after
- *                  yh_loss_dense on the same workspace and after yh_assign.
+ *   yh_loss_dense         the objectness BCE over all B*N cells against target 0 and, if
+ *                         grad_heads, the whole head gradient (zeros + sigmoid(x)*w/(B*N)).
+ *                         Needs only the heads: may run concurrently with yh_assign / yh_decode /
+ *                         yh_nms / yh_loss_rows_compute on other streams.
+ *   yh_loss_rows_compute  the M matched rows (box metric, class BCE, objectness correction);
+ *                         with want_grad their gradients are staged in the workspace
+ *                         ([M, 5+C]).  Ordered after yh_assign only.
+ *   yh_loss_finish        ordered after BOTH of the above on the same workspace (same capacity
+ *                         and cfg): scatters the staged row gradients over the dense gradient
+ *                         (grad_heads, NULL = forward only) and reduces all partial sums, in a
+ *                         fixed order, into losses4_dev.
+ *   yh_loss_rows          == yh_loss_rows_compute; yh_loss_finish on one stream (after dense).
  * yh_loss_fwd_bwd == yh_loss_dense; yh_loss_rows on one stream. */
 int yh_loss_dense(YhWorkspace* ws, const float* const* heads, const YhLayer* layers, int L, int B,
                   int C, const YhLossCfg* cfg, float* const* grad_heads, void* stream);
@@ -165,6 +175,15 @@ int yh_loss_rows(YhWorkspace* ws, const float* const* heads, const YhLayer* laye
                  const int64_t* m_class, const int32_t* M_dev, int capacity, const YhLossCfg* cfg,
                  float* losses4_dev, float* iou_score_dev, float* pred_rows_dev,
                  float* const* grad_heads, void* stream);
+int yh_loss_rows_compute(YhWorkspace* ws, const float* const* heads, const YhLayer* layers, int L,
+                         int B, int C, const int64_t* m_batch, const int64_t* m_flat,
+                         const float* m_target, const int64_t* m_class, const int32_t* M_dev,
+                         int capacity, const YhLossCfg* cfg, float* iou_score_dev,
+                         float* pred_rows_dev, int want_grad, void* stream);
+int yh_loss_finish(YhWorkspace* ws, const YhLayer* layers, int L, int B, int C,
+                   const int64_t* m_batch, const int64_t* m_flat, const int32_t* M_dev,
+                   int capacity, const YhLossCfg* cfg, float* losses4_dev,
+                   float* const* grad_heads, void* stream);
 
 /* ---- a12+a13: NonMaxSuppression::forward (`yolo-dl/src/loss/nms.rs:72-170`) incl. the
  * grouped greedy NMS of tch_nms::nms_by_scores (call site nms.rs:142-148).
@@ -259,6 +278,10 @@ int64_t yh_launch_count(int reset);
  * read. */
 #define YH_NUM_KERNELS 13
 int yh_timing_enable(int on);
+/* Debug aid: while dev_buf (2 * number-of-kernel-ids uint64, device) is set on this thread, every
+ * launch is bracketed by one-thread kernels that write %globaltimer (ns) to dev_buf[2*id] and
+ * dev_buf[2*id+1]; capturable into a CUDA graph.  NULL disables. */
+int yh_trace_enable(unsigned long long* dev_buf);
 int yh_timing_read(double* ms_sum, int64_t* launches, int n);
 
 #ifdef __cplusplus

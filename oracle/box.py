@@ -83,4 +83,24 @@ def ciou_with(p, q):
     return iou - center_dist_square / diagonal_square + shape_loss_coef * shape_loss
 
 
+def hausdorff_distance_to(p, q):
+    """CyCxHWTensor::hausdorff_distance_to (cycxhw.rs:122-125) -> TLBRTensor::hausdorff_distance_to
+    (tlbr.rs:137-177): self = p, other = q; `pow(&Tensor::from(2i64))` = pow with a 0-dim int64
+    tensor exponent; `max_other` = torch.maximum."""
+    tl, ll, bl, rl = tlbr_of(*p)
+    tr, lr, br, rr = tlbr_of(*q)
+    dt = tr - tl
+    dl = lr - ll
+    db = bl - br
+    dr = rl - rr
+    dt_l, dl_l, db_l, dr_l = (x.clamp_min(0.0) for x in (dt, dl, db, dr))
+    dt_r, dl_r, db_r, dr_r = ((-x).clamp_min(0.0) for x in (dt, dl, db, dr))
+    two = torch.tensor(2, dtype=torch.int64)
+    out = dt_l.pow(two) + dl_l.pow(two)
+    for a, b in ((dt_l, dr_l), (db_l, dl_l), (db_l, dr_l), (dt_r, dl_r), (dt_r, dr_r), (db_r, dl_r),
+                 (db_r, dr_r)):
+        out = torch.maximum(out, a.pow(two) + b.pow(two))
+    return out.sqrt()
+
+
 METRICS = {"iou": iou_with, "giou": giou_with, "diou": diou_with, "ciou": ciou_with}

@@ -49,8 +49,13 @@ def yolo_loss_from_matches(merged: dict, batches, flats, target_cycxhw, target_c
     q = tuple(target_cycxhw[:, i:i + 1] for i in range(4))
 
     # iou_loss (:279-322)
-    iou_score = obox.METRICS[cfg.box_metric](p, q)
-    iou_loss = 1.0 - iou_score
+    if cfg.box_metric == "hausdorff":  # (:285-288): the distance is the loss, no score
+        iou_score = None
+        iou_loss = obox.hausdorff_distance_to(p, q)
+    else:
+        iou_score = obox.METRICS[cfg.box_metric](p, q)
+        iou_loss = 1.0 - iou_score
+    per_row = iou_loss
     if cfg.reduction == "mean":
         iou_loss = iou_loss.mean() if M > 0 else torch.zeros((), dtype=torch.float32, device=dev)
     else:
@@ -71,7 +76,8 @@ def yolo_loss_from_matches(merged: dict, batches, flats, target_cycxhw, target_c
     with torch.no_grad():
         target_scores = torch.full((M, 1), 1.0 - cfg.smooth_objectness_coef, dtype=torch.float32,
                                    device=dev)
-        target_scores += iou_score.detach().clamp(0.0, 1.0) * cfg.smooth_objectness_coef
+        if iou_score is not None:  # (:401-404)
+            target_scores += iou_score.detach().clamp(0.0, 1.0) * cfg.smooth_objectness_coef
         target_obj = torch.zeros_like(pred_obj)
         # index_put_(&[Some(batches), None, Some(flats)], target_scores, false) (:409-414)
         target_obj[batches, :, flats] = target_scores
@@ -83,6 +89,8 @@ def yolo_loss_from_matches(merged: dict, batches, flats, target_cycxhw, target_c
     total = (cfg.iou_loss_weight * iou_loss + cfg.classification_loss_weight * cls_loss
              + cfg.objectness_loss_weight * obj_loss)  # (:258-260)
     losses = dict(total=total, iou=iou_loss, classification=cls_loss, objectness=obj_loss)
+    if iou_score is None:  # callers compare per-row values: hand back the distances
+        iou_score = per_row
     return losses, iou_score, pred, target_dense, target_obj
 
 

@@ -42,7 +42,8 @@ def _compare(heads, out, aux, ref, what):
     assert np.array_equal(aux.matchings.pred_indexes.flats.cpu().numpy(), ref["matches"][1])
     # box metric per matched row: |a-b| <= 1e-5 (scores live in [-2,2]; relative error is
     # unbounded at the zero crossings of GIoU/DIoU/CIoU)
-    close(aux.iou_score, ref["iou_score"], rtol=1e-5, atol=1e-5, what=f"{what} iou_score")
+    if aux.iou_score is not None:
+        close(aux.iou_score, ref["iou_score"], rtol=1e-5, atol=1e-5, what=f"{what} iou_score")
     p = aux.matchings.pred
     close(p.cycxhw.cy, ref["pred"]["cy"], what="pred cy")
     close(p.cycxhw.w, ref["pred"]["w"], what="pred w")
@@ -51,7 +52,7 @@ def _compare(heads, out, aux, ref, what):
         grad_close(h.grad, g, what=f"{what} grad layer {l}")
 
 
-@pytest.mark.parametrize("metric", ["iou", "giou", "diou", "ciou"])
+@pytest.mark.parametrize("metric", ["iou", "giou", "diou", "ciou", "hausdorff"])
 def test_loss_small_all_metrics(dev, metric):
     spec = synth.small_spec()
     targets = synth.make_targets(spec, 4, 31, n_max=8, clustered=0.3, adversarial=True)
@@ -66,6 +67,17 @@ def test_loss_yolov4_608_batch8(dev, metric):
     targets = synth.make_targets(spec, 8, synth.SEED0 + 1)
     heads, out, aux, ref = _run(dev, spec, 8, targets, seed=synth.SEED0 + 1, box_metric=metric)
     _compare(heads, out, aux, ref, f"608 {metric}")
+
+
+def test_loss_hausdorff_yolov4_608_and_no_score(dev):
+    """BoxMetric::Hausdorff (loss_.rs:285-288): the distance is the loss, the auxiliary score is
+    None and objectness smoothing falls back to the constant 1 - s_o."""
+    spec = synth.yolov4_608()
+    targets = synth.make_targets(spec, 4, 19, n_max=30)
+    heads, out, aux, ref = _run(dev, spec, 4, targets, box_metric="hausdorff",
+                                smooth_objectness_coef=0.2)
+    assert aux.iou_score is None
+    _compare(heads, out, aux, ref, "hausdorff 608")
 
 
 def test_loss_options_sum_smoothing_posweight(dev):

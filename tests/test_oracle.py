@@ -209,3 +209,42 @@ def test_nms_forward_and_pick_on_yolov4_608():
     p = onms.inference_pick(a)
     pairs = list(zip(p["batches"].tolist(), p["instances"].tolist()))
     assert len(pairs) == len(set(pairs)) and len(pairs) <= len(a["batches"])
+
+
+def test_hausdorff_known_answers():
+    """TLBRTensor::hausdorff_distance_to (tlbr.rs:137-177): hand-computed cases.  The reference's
+    formula is the largest corner-to-corner displacement over the four corners, taken separately
+    for the 'pred inside' and 'pred outside' signs."""
+    from oracle import box as obox
+
+    def t(*rows):
+        a = torch.tensor(rows, dtype=torch.float32)
+        return tuple(a[:, i:i + 1] for i in range(4))
+
+    # identical boxes -> 0 ; same size shifted by (dy,dx)=(0.3,-0.4) -> 0.5
+    p = t((0.5, 0.5, 0.2, 0.2), (0.5, 0.5, 0.2, 0.2), (0.5, 0.5, 0.2, 0.2))
+    q = t((0.5, 0.5, 0.2, 0.2), (0.8, 0.1, 0.2, 0.2), (0.5, 0.5, 0.6, 0.4))
+    d = obox.hausdorff_distance_to(p, q).view(-1)
+    assert float(d[0]) == 0.0
+    assert abs(float(d[1]) - 0.5) < 1e-6
+    # concentric, target larger by 0.2 per side in y and 0.1 in x -> sqrt(0.2^2 + 0.1^2)
+    assert abs(float(d[2]) - (0.2 ** 2 + 0.1 ** 2) ** 0.5) < 1e-6
+    # independent numpy restatement on random boxes
+    g = torch.Generator().manual_seed(5)
+    a = torch.rand(200, 4, generator=g) * 0.5 + 0.1
+    b = torch.rand(200, 4, generator=g) * 0.5 + 0.1
+    got = obox.hausdorff_distance_to(tuple(a[:, i:i + 1] for i in range(4)),
+                                     tuple(b[:, i:i + 1] for i in range(4))).view(-1).numpy()
+    an, bn = a.numpy().astype(np.float64), b.numpy().astype(np.float64)
+
+    def edges(x):
+        return x[:, 0] - x[:, 2] / 2, x[:, 1] - x[:, 3] / 2, x[:, 0] + x[:, 2] / 2, x[:, 1] + x[:, 3] / 2
+    pt, pl, pb, pr = edges(an)
+    qt, ql, qb, qr = edges(bn)
+    dd = [qt - pt, ql - pl, pb - qb, pr - qr]
+    best = np.zeros(200)
+    for sgn in (1.0, -1.0):
+        c = [np.maximum(sgn * x, 0.0) for x in dd]
+        for i, j in ((0, 1), (0, 3), (2, 1), (2, 3)):
+            best = np.maximum(best, c[i] ** 2 + c[j] ** 2)
+    assert np.allclose(got, np.sqrt(best), rtol=1e-5, atol=1e-6)

@@ -61,6 +61,12 @@ SYMBOLS = {
     "yh_loss_rows": (c_int, [c_void_p, _PF, POINTER(YhLayer), c_int, c_int, c_int, c_void_p,
                              c_void_p, c_void_p, c_void_p, c_void_p, c_int, POINTER(YhLossCfg),
                              c_void_p, c_void_p, c_void_p, _PF, c_void_p]),
+    "yh_loss_rows_compute": (c_int, [c_void_p, _PF, POINTER(YhLayer), c_int, c_int, c_int, c_void_p,
+                                     c_void_p, c_void_p, c_void_p, c_void_p, c_int, POINTER(YhLossCfg),
+                                     c_void_p, c_void_p, c_int, c_void_p]),
+    "yh_loss_finish": (c_int, [c_void_p, POINTER(YhLayer), c_int, c_int, c_int, c_void_p, c_void_p,
+                               c_void_p, c_int, POINTER(YhLossCfg), c_void_p, _PF, c_void_p]),
+    "yh_workspace_reserve_rows": (c_int, [c_void_p, c_int, c_int]),
     "yh_nms": (c_int, [c_void_p, _PF, POINTER(YhLayer), c_int, c_int, c_int, c_double, c_double,
                        c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
                        c_void_p]),
@@ -78,13 +84,14 @@ SYMBOLS = {
                                c_void_p]),
     "yh_launch_count": (c_int64, [c_int]),
     "yh_timing_enable": (c_int, [c_int]),
+    "yh_trace_enable": (c_int, [c_void_p]),
     "yh_timing_read": (c_int, [POINTER(c_double), POINTER(c_int64), c_int]),
 }
 
 KERNEL_NAMES = ["decode_kernel", "assign_slots_kernel", "assign_emit_kernel", "loss_dense_kernel",
                 "loss_rows_kernel", "nms_filter_kernel", "nms_segment_kernel", "nms_emit_kernel",
                 "nms_pack_kernel", "pick_kernel", "benchmark_kernel",
-                "match_det_gt_kernel", "ap_kernel"]
+                "match_det_gt_kernel", "ap_kernel", "loss_finish_kernel"]
 
 _lib = None
 

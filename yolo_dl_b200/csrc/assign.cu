@@ -12,7 +12,7 @@
 // = "smallest distance, then earliest GT", exactly the fold's result for any entry order.
 // All decisions use f64 and the reference's operation order; products and sums are written
 // with __dmul_rn/__dadd_rn so no FMA can change a floor(), a '< 0.5' or a distance tie.
-// A second kernel turns the slot table into the (batch, flat)-sorted match list.
+// A second kernel turns the occupied slots into the (batch, flat)-sorted match list.
 #include <math.h>
 
 #include "common.cuh"
@@ -68,23 +68,32 @@ __device__ __forceinline__ void for_each_cell(const AssignTab& t, int l, int a, 
   }
 }
 
+// Slot-table invariant: between two yh_assign calls every slot of the workspace is EMPTY
+// (dist = ~0, gt = kEmptyGt; set once by yh_workspace_create).  A call touches only the slots
+// its entries fall into (~10..15 per GT), records them in a per-image occupancy bitmap and the
+// emit kernel puts them back to EMPTY after reading them — no O(N) initialisation or scan of
+// the table per image, which is what made the first version of this path 58 us per step.
+constexpr int kEmptyGt = 0x7f7f7f7f;  // cudaMemset(0x7f)
+constexpr int kBitsSmem = 2048;       // occupancy words kept in shared memory (65536 instances)
+
 __global__ void __launch_bounds__(kAssignThreads)
 assign_slots_kernel(const AssignTab t, const double* __restrict__ gt,
                     const int* __restrict__ gt_off, unsigned long long* __restrict__ slot_dist,
-                    int* __restrict__ slot_gt, int* __restrict__ img_count) {
+                    int* __restrict__ slot_gt, unsigned* __restrict__ slot_bits, const int words,
+                    int* __restrict__ img_count) {
   __shared__ double s_gt[kMaxGtSmem][4];
+  __shared__ unsigned s_bits[kBitsSmem];
   __shared__ int s_cnt[kAssignThreads / 32];
   const int b = blockIdx.x;
   const int g0 = gt_off[b], g1 = gt_off[b + 1];
   const int ng = g1 - g0;
   unsigned long long* sd = slot_dist + (size_t)b * (size_t)t.N;
   int* sg = slot_gt + (size_t)b * (size_t)t.N;
+  unsigned* gbits = slot_bits + (size_t)b * (size_t)words;
+  const bool in_smem = words <= kBitsSmem;
+  unsigned* bits = in_smem ? s_bits : gbits;  // generic pointer: atomicOr works on either
 
-  for (int i = threadIdx.x; i < t.N; i += kAssignThreads) {
-    sd[i] = ~0ull;
-    sg[i] = 0x7fffffff;
-  }
-  __syncthreads();
+  for (int i = threadIdx.x; i < words; i += kAssignThreads) bits[i] = 0u;
 
   // total anchors over layers, and prefix for (layer, anchor) enumeration
   int la_total = 0;
@@ -111,7 +120,10 @@ assign_slots_kernel(const AssignTab t, const double* __restrict__ gt,
         const int gidx = base + g;
         if (pass == 0) {
           for_each_cell(t, l, r, s_gt[g][0], s_gt[g][1], gh, gw,
-                        [&](int flat, unsigned long long d) { atomicMin(&sd[flat], d); });
+                        [&](int flat, unsigned long long d) {
+                          atomicMin(&sd[flat], d);
+                          atomicOr(&bits[flat >> 5], 1u << (flat & 31));
+                        });
         } else {
           for_each_cell(t, l, r, s_gt[g][0], s_gt[g][1], gh, gw,
                         [&](int flat, unsigned long long d) {
@@ -123,10 +135,13 @@ assign_slots_kernel(const AssignTab t, const double* __restrict__ gt,
     __syncthreads();
   }
 
-  // matches of this image
+  // matches of this image = occupied slots; publish the bitmap for the emit kernel
   int local = 0;
-  for (int i = threadIdx.x; i < t.N; i += kAssignThreads)
-    local += (__ldcg(&sg[i]) != 0x7fffffff) ? 1 : 0;
+  for (int i = threadIdx.x; i < words; i += kAssignThreads) {
+    const unsigned w = bits[i];
+    local += __popc(w);
+    if (in_smem) gbits[i] = w;
+  }
   for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
   if ((threadIdx.x & 31) == 0) s_cnt[threadIdx.x >> 5] = local;
   __syncthreads();
@@ -137,28 +152,34 @@ assign_slots_kernel(const AssignTab t, const double* __restrict__ gt,
   }
 }
 
-// Ordered compaction of the slot table into the match list, sorted by (batch, flat).
-__global__ void __launch_bounds__(kAssignThreads)
-assign_emit_kernel(int N, int B, const double* __restrict__ gt, const int* __restrict__ gt_off,
-                   const int* __restrict__ slot_gt, const int* __restrict__ img_count,
-                   long long* __restrict__ out_batch, long long* __restrict__ out_flat,
-                   int* __restrict__ out_gt, float* __restrict__ out_target,
-                   long long* __restrict__ out_class, int* __restrict__ out_M, int capacity,
-                   int* __restrict__ err_flag) {
-  __shared__ int s_warp[kAssignThreads / 32];
+// Ordered compaction of the occupied slots into the match list, sorted by (batch, flat);
+// puts every slot it reads back to EMPTY.
+constexpr int kEmitThreads = 256;
+constexpr int kEmitList = 2048;  // matches of one tile (256 words = 8192 instances) kept in smem
+
+__global__ void __launch_bounds__(kEmitThreads)
+assign_emit_kernel(int N, int B, const int words, const double* __restrict__ gt,
+                   const int* __restrict__ gt_off, unsigned long long* __restrict__ slot_dist,
+                   int* __restrict__ slot_gt, const unsigned* __restrict__ slot_bits,
+                   const int* __restrict__ img_count, long long* __restrict__ out_batch,
+                   long long* __restrict__ out_flat, int* __restrict__ out_gt,
+                   float* __restrict__ out_target, long long* __restrict__ out_class,
+                   int* __restrict__ out_M, int capacity, int* __restrict__ err_flag) {
+  __shared__ int s_warp[kEmitThreads / 32];
   __shared__ int s_base;
+  __shared__ int s_list[kEmitList];
   const int b = blockIdx.x;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
 
   // offset of this image = sum of counts of earlier images
   int part = 0;
-  for (int i = threadIdx.x; i < b; i += kAssignThreads) part += img_count[i];
+  for (int i = threadIdx.x; i < b; i += kEmitThreads) part += img_count[i];
   for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
   if (lane == 0) s_warp[wid] = part;
   __syncthreads();
   if (threadIdx.x == 0) {
     int tot = 0;
-    for (int i = 0; i < kAssignThreads / 32; ++i) tot += s_warp[i];
+    for (int i = 0; i < kEmitThreads / 32; ++i) tot += s_warp[i];
     s_base = tot;
     if (b == B - 1) {
       const int M = tot + img_count[b];
@@ -168,36 +189,72 @@ assign_emit_kernel(int N, int B, const double* __restrict__ gt, const int* __res
   }
   __syncthreads();
   int base = s_base;
+  if (img_count[b] == 0) return;  // block-uniform
   const int g0 = gt_off[b];
-  const int* sg = slot_gt + (size_t)b * (size_t)N;
+  unsigned long long* sd = slot_dist + (size_t)b * (size_t)N;
+  int* sg = slot_gt + (size_t)b * (size_t)N;
+  const unsigned* bits = slot_bits + (size_t)b * (size_t)words;
 
-  for (int tile = 0; tile < N; tile += kAssignThreads) {
-    const int i = tile + threadIdx.x;
-    const int g = (i < N) ? sg[i] : 0x7fffffff;
-    const bool hit = g != 0x7fffffff;
-    const unsigned m = __ballot_sync(0xffffffffu, hit);
+  for (int tile = 0; tile < words; tile += kEmitThreads) {
+    const int wi = tile + threadIdx.x;
+    unsigned w = (wi < words) ? bits[wi] : 0u;
+    const int c = __popc(w);
+    // exclusive scan of c over the CTA
+    int incl = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
     __syncthreads();  // s_warp reuse
-    if (lane == 0) s_warp[wid] = __popc(m);
+    if (lane == 31) s_warp[wid] = incl;
     __syncthreads();
     int before = 0, total = 0;
 #pragma unroll
-    for (int k = 0; k < kAssignThreads / 32; ++k) {
-      const int c = s_warp[k];
-      if (k < wid) before += c;
-      total += c;
+    for (int k = 0; k < kEmitThreads / 32; ++k) {
+      const int v = s_warp[k];
+      if (k < wid) before += v;
+      total += v;
     }
-    if (hit) {
-      const int pos = base + before + __popc(m & ((1u << lane) - 1u));
+    // publish the flats of this tile in order, then one thread per match (no serial walk over
+    // the bits of a word: every match costs two dependent L2 round trips, slot -> GT row)
+    int lp = before + incl - c;
+    while (w) {
+      const int bit = __ffs(w) - 1;
+      w &= w - 1;
+      if (lp < kEmitList) s_list[lp] = wi * 32 + bit;
+      ++lp;
+    }
+    __syncthreads();
+    for (int j = threadIdx.x; j < total; j += kEmitThreads) {
+      int flat;
+      if (total <= kEmitList) {
+        flat = s_list[j];
+      } else {
+        // overflow of the list (> kEmitList matches in 8192 instances): select the j-th set bit
+        int rem = j, k = tile;
+        for (;; ++k) {
+          const int pc = __popc(bits[k]);
+          if (rem < pc) break;
+          rem -= pc;
+        }
+        unsigned ww = bits[k];
+        for (int r = 0; r < rem; ++r) ww &= ww - 1;
+        flat = k * 32 + __ffs(ww) - 1;
+      }
+      const int pos = base + j;
+      const int g = sg[flat];
+      sg[flat] = kEmptyGt;
+      sd[flat] = ~0ull;
       if (pos < capacity) {
         const int grow = g0 + g;
         out_batch[pos] = b;
-        out_flat[pos] = i;
+        out_flat[pos] = flat;
         out_gt[pos] = grow;
         const double* r = gt + (size_t)grow * 5;
-        out_target[(size_t)pos * 4 + 0] = (float)r[0];  // rect.cast::<f32>() (:247)
-        out_target[(size_t)pos * 4 + 1] = (float)r[1];
-        out_target[(size_t)pos * 4 + 2] = (float)r[2];
-        out_target[(size_t)pos * 4 + 3] = (float)r[3];
+        // rect.cast::<f32>() (:247)
+        *reinterpret_cast<float4*>(out_target + (size_t)pos * 4) =
+            make_float4((float)r[0], (float)r[1], (float)r[2], (float)r[3]);
         out_class[pos] = (long long)r[4];
       }
     }
@@ -221,6 +278,7 @@ extern "C" int yh_assign(YhWorkspace* ws, const double* gt_dev, const int32_t* g
   // CyCxHWMatcherInit::build (:32-35)
   YH_REQUIRE(anchor_scale_thresh >= 1.0, "anchor_scale_thresh must be greater than or equal to 1");
   YH_REQUIRE(capacity >= 0, "capacity=%d", capacity);
+  YH_REQUIRE(((uintptr_t)out_target & 15) == 0, "out_target not 16-byte aligned");
   LayerTab lt;
   int rc = build_layer_tab(layers, L, 1, nullptr, &lt);
   if (rc) return rc;
@@ -244,12 +302,15 @@ extern "C" int yh_assign(YhWorkspace* ws, const double* gt_dev, const int32_t* g
   cudaStream_t s = (cudaStream_t)stream;
   YH_CUDA(cudaSetDevice(ws->device));
   YH_TIME(YH_K_ASSIGN_SLOTS, s);
+  const int words = (t.N + 31) / 32;
   assign_slots_kernel<<<B, kAssignThreads, 0, s>>>(t, gt_dev, gt_offsets_dev, ws->slot_dist,
-                                                   ws->slot_gt, ws->img_count);
+                                                   ws->slot_gt, ws->slot_bits, words,
+                                                   ws->img_count);
   YH_LAUNCHED(s);
   YH_TIME(YH_K_ASSIGN_EMIT, s);
-  assign_emit_kernel<<<B, kAssignThreads, 0, s>>>(
-      t.N, B, gt_dev, gt_offsets_dev, ws->slot_gt, ws->img_count, (long long*)out_batch,
+  assign_emit_kernel<<<B, kEmitThreads, 0, s>>>(
+      t.N, B, words, gt_dev, gt_offsets_dev, ws->slot_dist, ws->slot_gt, ws->slot_bits,
+      ws->img_count, (long long*)out_batch,
       (long long*)out_flat, out_gt, out_target, (long long*)out_class, out_M_dev, capacity,
       ws->err_flag);
   YH_LAUNCHED(s);

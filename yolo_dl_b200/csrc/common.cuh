@@ -43,7 +43,7 @@ int64_t& launch_counter();
 enum KernelId {
   YH_K_DECODE = 0, YH_K_ASSIGN_SLOTS, YH_K_ASSIGN_EMIT, YH_K_LOSS_DENSE, YH_K_LOSS_ROWS,
   YH_K_NMS_FILTER, YH_K_NMS_SEGMENT, YH_K_NMS_EMIT, YH_K_NMS_PACK, YH_K_PICK, YH_K_BENCHMARK,
-  YH_K_MATCH_DET_GT, YH_K_AP, YH_K_COUNT
+  YH_K_MATCH_DET_GT, YH_K_AP, YH_K_LOSS_FINISH, YH_K_COUNT
 };
 void timing_begin(int id, cudaStream_t s);  // no-ops unless timing is enabled on this thread
 void timing_end(cudaStream_t s);
@@ -76,6 +76,10 @@ struct LayerTab {
 // Validates the layers and fills tab (host). heads may be NULL (then tab.head is NULL).
 int build_layer_tab(const YhLayer* layers, int L, int C, const float* const* heads,
                     LayerTab* tab);
+
+// Grows ws->row_grad to `floats` (no-op when large enough).  Allocation is not possible while
+// `s` is being captured into a CUDA graph: reserve first (yh_workspace_reserve_rows).
+int reserve_rows(YhWorkspace* ws, size_t floats, cudaStream_t s);
 
 // Position of a flat instance index inside its layer.
 struct Cell {
@@ -150,14 +154,18 @@ struct YhWorkspace {
   int cand_per_image;
   int num_sms;
 
-  // assignment (assign.cu): per (image, flat) slot
+  // assignment (assign.cu): per (image, flat) slot; EMPTY (~0 / 0x7f7f7f7f) between calls
   unsigned long long* slot_dist;  // [max_batch * max_instances] f64 bits of best dist^2
   int* slot_gt;                   // [max_batch * max_instances] winning GT (local index)
+  unsigned* slot_bits;            // [max_batch * ceil(max_instances/32)] occupancy bitmap
   int* img_count;                 // [max_batch] matches per image
+  unsigned long long* pick_slot;  // [max_batch * max_instances] scratch of yh_inference_pick
 
   // loss (loss.cu)
   double* partials;               // [YH_PARTIALS_MAX * 4]
   unsigned int* ticket;           // last-block-done counter
+  float* row_grad;                // [row_grad_floats] staged gradients of the matched rows [M, 5+C]
+  size_t row_grad_floats;
 
   // nms (nms.cu): per-image regions of cand_stride (= next pow2 of cand_per_image) entries
   long long cand_stride;

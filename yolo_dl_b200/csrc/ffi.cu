@@ -40,7 +40,25 @@ static cudaEvent_t get_event() {
   return e;
 }
 
+// ---- optional in-graph trace: a one-thread kernel before and after every launch writes
+// %globaltimer into trace[2*id], trace[2*id+1]; unlike events it can be captured into a CUDA
+// graph, so it shows where each kernel really runs inside the overlapped, replayed step
+// (tools/timeline.py).  Debug aid only.
+static thread_local unsigned long long* g_trace = nullptr;
+static thread_local int g_trace_id = 0;
+
+__global__ void stamp_kernel(unsigned long long* slot) {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  *slot = t;
+}
+
 void timing_begin(int id, cudaStream_t s) {
+  if (g_trace) {
+    g_trace_id = id;
+    stamp_kernel<<<1, 1, 0, s>>>(g_trace + 2 * id);
+    return;
+  }
   if (!g_timing) return;
   if (!g_timed) g_timed = new std::vector<TimedLaunch>();
   TimedLaunch t;
@@ -52,6 +70,10 @@ void timing_begin(int id, cudaStream_t s) {
 }
 
 void timing_end(cudaStream_t s) {
+  if (g_trace) {
+    stamp_kernel<<<1, 1, 0, s>>>(g_trace + 2 * g_trace_id + 1);
+    return;
+  }
   if (!g_timing || !g_timed || g_timed->empty()) return;
   cudaEventRecord(g_timed->back().b, s);
 }
@@ -94,9 +116,36 @@ int build_layer_tab(const YhLayer* layers, int L, int C, const float* const* hea
   return YH_OK;
 }
 
+int reserve_rows(YhWorkspace* ws, size_t floats, cudaStream_t s) {
+  if (floats <= ws->row_grad_floats) return YH_OK;
+  cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(s, &st) != cudaSuccess) {
+    cudaGetLastError();
+    st = cudaStreamCaptureStatusNone;
+  }
+  YH_REQUIRE(st == cudaStreamCaptureStatusNone,
+             "row-gradient staging (%zu floats) must be reserved before stream capture: call "
+             "yh_workspace_reserve_rows(ws, capacity, C) first", floats);
+  YH_CUDA(cudaSetDevice(ws->device));
+  // the old buffer may still be in use by work already enqueued on this device
+  YH_CUDA(cudaDeviceSynchronize());
+  if (ws->row_grad) YH_CUDA(cudaFree(ws->row_grad));
+  ws->row_grad = nullptr;
+  ws->row_grad_floats = 0;
+  YH_CUDA(cudaMalloc((void**)&ws->row_grad, floats * sizeof(float)));
+  ws->row_grad_floats = floats;
+  return YH_OK;
+}
+
 }  // namespace yh
 
 extern "C" {
+
+int yh_workspace_reserve_rows(YhWorkspace* ws, int capacity, int C) {
+  YH_REQUIRE(ws != nullptr, "workspace is NULL");
+  YH_REQUIRE(capacity >= 0 && C >= 1, "capacity=%d C=%d", capacity, C);
+  return yh::reserve_rows(ws, (size_t)capacity * (size_t)(5 + C), nullptr);
+}
 
 const char* yh_last_error(void) { return yh::g_err; }
 
@@ -106,6 +155,11 @@ int64_t yh_launch_count(int reset) {
   int64_t v = yh::g_launches;
   if (reset) yh::g_launches = 0;
   return v;
+}
+
+int yh_trace_enable(unsigned long long* dev_buf) {
+  yh::g_trace = dev_buf;
+  return YH_OK;
 }
 
 int yh_timing_enable(int on) {
@@ -141,9 +195,12 @@ int yh_workspace_destroy(YhWorkspace* ws) {
   cudaSetDevice(ws->device);
   cudaFree(ws->slot_dist);
   cudaFree(ws->slot_gt);
+  cudaFree(ws->slot_bits);
   cudaFree(ws->img_count);
+  cudaFree(ws->pick_slot);
   cudaFree(ws->partials);
   cudaFree(ws->ticket);
+  cudaFree(ws->row_grad);
   cudaFree(ws->cand_key);
   cudaFree(ws->cand_count);
   cudaFree(ws->kept_key);
@@ -205,7 +262,9 @@ int yh_workspace_create(int device, int max_batch, int64_t max_instances, int ca
   } while (0)
   YH_ALLOC(ws->slot_dist, slots * sizeof(unsigned long long));
   YH_ALLOC(ws->slot_gt, slots * sizeof(int));
+  YH_ALLOC(ws->slot_bits, (size_t)max_batch * (size_t)((max_instances + 31) / 32) * sizeof(unsigned));
   YH_ALLOC(ws->img_count, (size_t)max_batch * sizeof(int));
+  YH_ALLOC(ws->pick_slot, slots * sizeof(unsigned long long));
   YH_ALLOC(ws->partials, (size_t)YH_PARTIALS_MAX * 4 * sizeof(double));
   YH_ALLOC(ws->ticket, 64);
   YH_ALLOC(ws->cand_key, cands * sizeof(unsigned long long));
@@ -216,7 +275,10 @@ int yh_workspace_create(int device, int max_batch, int64_t max_instances, int ca
   YH_ALLOC(ws->kept_grp, cands * sizeof(long long));
   YH_ALLOC(ws->err_flag, 64);
 #undef YH_ALLOC
-  if (cudaMemset(ws->ticket, 0, 64) != cudaSuccess ||
+  // the matcher's slot table is EMPTY between calls (assign.cu)
+  if (cudaMemset(ws->slot_dist, 0xff, slots * sizeof(unsigned long long)) != cudaSuccess ||
+      cudaMemset(ws->slot_gt, 0x7f, slots * sizeof(int)) != cudaSuccess ||
+      cudaMemset(ws->ticket, 0, 64) != cudaSuccess ||
       cudaMemset(ws->err_flag, 0, 64) != cudaSuccess ||
       cudaMallocHost((void**)&ws->host_counts, ((size_t)max_batch + 8) * sizeof(int32_t)) !=
           cudaSuccess) {

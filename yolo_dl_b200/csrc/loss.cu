@@ -22,6 +22,7 @@
 // Reductions are deterministic: per-CTA partials in fixed slots, summed in a fixed order by
 // the last CTA of K3 (ticket counter), in f64.
 #include <math.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -358,6 +359,68 @@ __device__ __forceinline__ float box_metric(const int metric, const Box4 p, cons
   return m;
 }
 
+// Hausdorff distance between two boxes (tlbr.rs:137-177 via cycxhw.rs:122-125), forward and the
+// reverse mode of the same ATen chain: clamp_min passes the gradient where its input >= 0,
+// pow(2) gives 2x, maximum gives everything to the larger operand and half to each on a tie
+// (ties are the common case here: most clamped differences are 0), sqrt gives g/(2*sqrt).
+// Returns the distance; if want_grad, d receives d(distance)/d(pred) * g.
+__device__ __forceinline__ float hausdorff_metric(const Box4 p, const Box4 q, const float g,
+                                                  const bool want_grad, Box4& d) {
+  const float pt = p.cy - p.h / 2.0f, pb = p.cy + p.h / 2.0f;
+  const float pl = p.cx - p.w / 2.0f, pr = p.cx + p.w / 2.0f;
+  const float qt = q.cy - q.h / 2.0f, qb = q.cy + q.h / 2.0f;
+  const float ql = q.cx - q.w / 2.0f, qr = q.cx + q.w / 2.0f;
+  // self = pred, other = target: dt = tr - tl, dl = lr - ll, db = bl - br, dr = rl - rr
+  const float dv[4] = {qt - pt, ql - pl, pb - qb, pr - qr};  // t, l, b, r
+  float cl[4], cr[4];                                        // clamp_min(d,0), clamp_min(-d,0)
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    cl[k] = fmaxf(dv[k], 0.0f);
+    cr[k] = fmaxf(-dv[k], 0.0f);
+  }
+  // the eight corner terms in the reference's order: (t,l) (t,r) (b,l) (b,r), _l then _r
+  const int ia[4] = {0, 0, 2, 2}, ib[4] = {1, 3, 1, 3};
+  float T[8];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    T[k] = cl[ia[k]] * cl[ia[k]] + cl[ib[k]] * cl[ib[k]];
+    T[4 + k] = cr[ia[k]] * cr[ia[k]] + cr[ib[k]] * cr[ib[k]];
+  }
+  float run[8];
+  run[0] = T[0];
+#pragma unroll
+  for (int k = 1; k < 8; ++k) run[k] = fmaxf(run[k - 1], T[k]);
+  const float dist = sqrtf(run[7]);
+  if (!want_grad) return dist;
+
+  float gT[8];
+  float gr = g / (2.0f * dist);  // sqrt backward
+#pragma unroll
+  for (int k = 7; k >= 1; --k) {
+    gT[k] = gr * w_gt(T[k], run[k - 1]);
+    gr = gr * w_gt(run[k - 1], T[k]);
+  }
+  gT[0] = gr;
+  float gcl[4] = {0.f, 0.f, 0.f, 0.f}, gcr[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    gcl[ia[k]] += gT[k] * (2.0f * cl[ia[k]]);
+    gcl[ib[k]] += gT[k] * (2.0f * cl[ib[k]]);
+    gcr[ia[k]] += gT[4 + k] * (2.0f * cr[ia[k]]);
+    gcr[ib[k]] += gT[4 + k] * (2.0f * cr[ib[k]]);
+  }
+  float gd[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+    gd[k] = (dv[k] >= 0.0f ? gcl[k] : 0.0f) - (-dv[k] >= 0.0f ? gcr[k] : 0.0f);
+  const float d_pt = -gd[0], d_pl = -gd[1], d_pb = gd[2], d_pr = gd[3];
+  d.cy = d_pt + d_pb;
+  d.h = (d_pb - d_pt) / 2.0f;
+  d.cx = d_pl + d_pr;
+  d.w = (d_pr - d_pl) / 2.0f;
+  return dist;
+}
+
 // ---------------------------------------------------------------------------------
 // K3
 // ---------------------------------------------------------------------------------
@@ -372,17 +435,17 @@ constexpr int kRowsPerWarp = 8;
 constexpr int kClsRegs = 3;
 
 __global__ void __launch_bounds__(kRowThreads)
-loss_rows_kernel(const LayerTab t, const GradTab g, const LossParams p,
+loss_rows_kernel(const LayerTab t, const LossParams p,
                  const long long* __restrict__ m_batch, const long long* __restrict__ m_flat,
                  const float* __restrict__ m_target, const long long* __restrict__ m_class,
                  const int* __restrict__ M_dev, const int capacity,
                  float* __restrict__ iou_score, float* __restrict__ pred_rows,
-                 double* __restrict__ partials, const int n_dense_partials,
-                 unsigned int* __restrict__ ticket, float* __restrict__ losses4) {
+                 float* __restrict__ row_grad, double* __restrict__ partials) {
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int warps = kRowThreads / 32;
   const int M = min(*M_dev, capacity);
-  const bool want_grad = g.grad[0] != nullptr;
+  const bool want_grad = row_grad != nullptr;
+  const bool haus = p.metric == YH_METRIC_HAUSDORFF;
   const float Mf = (float)M;
   const float MCf = (float)((long long)M * t.C);
   const float numel_obj = (float)((long long)p.B * t.N);
@@ -443,15 +506,17 @@ loss_rows_kernel(const LayerTab t, const GradTab g, const LossParams p,
       pb.w = decode_size(s3, t.aw[l][anchor]);
       Box4 tb;
       tb.cy = tg.x; tb.cx = tg.y; tb.h = tg.z; tb.w = tg.w;
-      // d total / d metric: total = w_iou * mean(1 - metric)
+      // d total / d metric: total = w_iou * mean(1 - metric); Hausdorff: w_iou * mean(distance)
       float gm = p.w_iou;
       if (p.reduction == YH_REDUCTION_MEAN) gm = gm / Mf;
-      gm = -gm;
+      if (!haus) gm = -gm;
       Box4 d = {0.f, 0.f, 0.f, 0.f};
-      const float metric = box_metric(p.metric, pb, tb, gm, want_grad, d);
-      a_iou += (double)(1.0f - metric);
-      // objectness target at this cell (loss_.rs:397-406)
-      const float to = p.obj_base + fminf(fmaxf(metric, 0.0f), 1.0f) * p.obj_coef;
+      const float metric = haus ? hausdorff_metric(pb, tb, gm, want_grad, d)
+                                : box_metric(p.metric, pb, tb, gm, want_grad, d);
+      a_iou += haus ? (double)metric : (double)(1.0f - metric);
+      // objectness target at this cell (loss_.rs:397-406); Hausdorff has no score (loss_.rs:285-288)
+      const float to = haus ? p.obj_base
+                            : p.obj_base + fminf(fmaxf(metric, 0.0f), 1.0f) * p.obj_coef;
       const float lwm1 = p.has_pw ? (p.pw - 1.0f) * to : 0.0f;
       a_obj += (double)(-to * xo) + (double)(lwm1 * softplus_f(-xo));
       if (iou_score) iou_score[m] = metric;
@@ -460,16 +525,17 @@ loss_rows_kernel(const LayerTab t, const GradTab g, const LossParams p,
         r[0] = pb.cy; r[1] = pb.cx; r[2] = pb.h; r[3] = pb.w; r[4] = xo;
       }
       if (want_grad) {
-        float* gp = g.grad[l] + off;
+        // staged per row ([M, 5+C], coalesced); loss_finish_kernel scatters it into the heads
+        float* gp = row_grad + (size_t)m * t.E;
         // chain through the decode (detect_2d.rs:69-72,122-133):
         //   cy = (2s-0.5)/H + off  -> dcy/ds = 2/H ; s' = s(1-s)
         //   h  = (2s)^2 * a        -> dh/ds  = a * 2*(2s) * 2
         const float Hf = (float)t.H[l], Wf = (float)t.W[l];
         gp[0] = (d.cy / Hf * 2.0f) * ((1.0f - s0) * s0);
-        gp[es] = (d.cx / Wf * 2.0f) * ((1.0f - s1) * s1);
-        gp[2 * (size_t)es] = ((d.h * t.ah[l][anchor]) * (2.0f * (s2 * 2.0f)) * 2.0f) * ((1.0f - s2) * s2);
-        gp[3 * (size_t)es] = ((d.w * t.aw[l][anchor]) * (2.0f * (s3 * 2.0f)) * 2.0f) * ((1.0f - s3) * s3);
-        // objectness gradient with the real target (overwrites K4's target-0 value)
+        gp[1] = (d.cx / Wf * 2.0f) * ((1.0f - s1) * s1);
+        gp[2] = ((d.h * t.ah[l][anchor]) * (2.0f * (s2 * 2.0f)) * 2.0f) * ((1.0f - s2) * s2);
+        gp[3] = ((d.w * t.aw[l][anchor]) * (2.0f * (s3 * 2.0f)) * 2.0f) * ((1.0f - s3) * s3);
+        // objectness gradient with the real target (replaces K4's target-0 value)
         const float so = sigmoid_f(xo);
         float gi;
         if (p.has_pw) {
@@ -479,7 +545,7 @@ loss_rows_kernel(const LayerTab t, const GradTab g, const LossParams p,
           gi = so - to;
         }
         if (p.reduction == YH_REDUCTION_MEAN) gi = gi / numel_obj;
-        gp[4 * (size_t)es] = gi * p.w_obj;
+        gp[4] = gi * p.w_obj;
       }
     }
 
@@ -492,7 +558,7 @@ loss_rows_kernel(const LayerTab t, const GradTab g, const LossParams p,
       const int cls_r = __shfl_sync(0xffffffffu, cls, r);
       if (m0 + r >= M) break;  // warp-uniform
       const float* hp = t.head[l_r] + off_r;
-      float* gp = want_grad ? g.grad[l_r] + off_r : nullptr;
+      float* gp = want_grad ? row_grad + (size_t)(m0 + r) * t.E : nullptr;
       float bce = 0.f;
       for (int k = lane, j = 0; k < t.C; k += 32, ++j) {
         float x;
@@ -505,7 +571,7 @@ loss_rows_kernel(const LayerTab t, const GradTab g, const LossParams p,
         if (want_grad) {
           float gi = sigmoid_f(x) - tt;
           if (p.reduction == YH_REDUCTION_MEAN) gi = gi / MCf;
-          gp[(size_t)(5 + k) * es_r] = gi * p.w_cls;
+          gp[5 + k] = gi * p.w_cls;
         }
         if (pred_rows) pred_rows[(size_t)(m0 + r) * t.E + 5 + k] = x;
       }
@@ -517,9 +583,8 @@ loss_rows_kernel(const LayerTab t, const GradTab g, const LossParams p,
   a_iou = warp_sum_d(a_iou);
   a_obj = warp_sum_d(a_obj);
 
-  // CTA partials -> fixed slot
+  // CTA partials -> fixed slot (summed in a fixed order by loss_finish_kernel)
   __shared__ double s_acc[kRowThreads / 32][3];
-  __shared__ bool s_last;
   if (lane == 0) {
     s_acc[wid][0] = a_iou;
     s_acc[wid][1] = a_cls;
@@ -537,38 +602,66 @@ loss_rows_kernel(const LayerTab t, const GradTab g, const LossParams p,
     dst[0] = s[0];
     dst[1] = s[1];
     dst[2] = s[2];
-    __threadfence();
-    const unsigned int prev = atomicAdd(ticket, 1u);
-    s_last = (prev == gridDim.x - 1);
   }
-  __syncthreads();
-  if (!s_last) return;
+}
 
-  // last CTA: fixed-order final sums
-  __threadfence();
-  __shared__ double s_red[kRowThreads][4];
+// ---------------------------------------------------------------------------------
+// K3b: ordered after K4 AND K3.  Scatters the staged row gradients into the head gradient
+// (overwriting K4's values at the matched cells: pure fire-and-forget 4-byte stores, a warp per
+// row, lanes across the 5+C entries) and, in CTA 0, sums all partials in a fixed order into the
+// four loss scalars.  Splitting this off K3 lets K3 (latency-bound gathers) run UNDER K4
+// (HBM-bound stream) instead of after it.
+// ---------------------------------------------------------------------------------
+constexpr int kFinishThreads = 256;
+
+__global__ void __launch_bounds__(kFinishThreads)
+loss_finish_kernel(const LayerTab t, const GradTab g, const LossParams p,
+                   const long long* __restrict__ m_batch, const long long* __restrict__ m_flat,
+                   const int* __restrict__ M_dev, const int capacity,
+                   const float* __restrict__ row_grad, const double* __restrict__ partials,
+                   const int n_dense_partials, const int n_row_partials,
+                   float* __restrict__ losses4) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int warps = kFinishThreads / 32;
+  const int M = min(*M_dev, capacity);
+  if (g.grad[0] != nullptr && row_grad != nullptr) {
+    for (int m = blockIdx.x * warps + wid; m < M; m += gridDim.x * warps) {
+      const int b = (int)__ldg(m_batch + m);
+      const int flat = (int)__ldg(m_flat + m);
+      const Cell c = locate(t, flat);
+      const int l = c.layer;
+      const size_t es = (size_t)t.A[l] * (size_t)t.HW[l];
+      float* gp = g.grad[l] + head_offset(t, l, b, c.anchor, c.cell);
+      const float* src = row_grad + (size_t)m * t.E;
+      for (int e = lane; e < t.E; e += 32) gp[(size_t)e * es] = __ldcs(src + e);
+    }
+  }
+  if (blockIdx.x != 0) return;
+
+  // CTA 0: fixed-order final sums
+  __shared__ double s_red[kFinishThreads][4];
   // every thread sums a strided subset; the loads of a thread are independent of its sums,
   // so they are issued kFinalUnroll at a time (the association is still a fixed one)
   constexpr int kFinalUnroll = 8;
   double r[4] = {0.0, 0.0, 0.0, 0.0};
-  for (int i0 = threadIdx.x; i0 < n_dense_partials; i0 += kRowThreads * kFinalUnroll) {
+  for (int i0 = threadIdx.x; i0 < n_dense_partials; i0 += kFinishThreads * kFinalUnroll) {
     double v[kFinalUnroll];
 #pragma unroll
     for (int u = 0; u < kFinalUnroll; ++u) {
-      const int i = i0 + u * kRowThreads;
+      const int i = i0 + u * kFinishThreads;
       v[u] = (i < n_dense_partials) ? __ldcg(&partials[(size_t)i * 4]) : 0.0;
     }
 #pragma unroll
     for (int u = 0; u < kFinalUnroll; ++u) r[3] += v[u];
   }
-  for (int i0 = threadIdx.x; i0 < (int)gridDim.x; i0 += kRowThreads * kFinalUnroll) {
+  for (int i0 = threadIdx.x; i0 < n_row_partials; i0 += kFinishThreads * kFinalUnroll) {
     double v[kFinalUnroll][3];
 #pragma unroll
     for (int u = 0; u < kFinalUnroll; ++u) {
-      const int i = i0 + u * kRowThreads;
+      const int i = i0 + u * kFinishThreads;
       const double* src = partials + (size_t)(kPartHalf + i) * 4;
 #pragma unroll
-      for (int k = 0; k < 3; ++k) v[u][k] = (i < (int)gridDim.x) ? __ldcg(&src[k]) : 0.0;
+      for (int k = 0; k < 3; ++k) v[u][k] = (i < n_row_partials) ? __ldcg(&src[k]) : 0.0;
     }
 #pragma unroll
     for (int u = 0; u < kFinalUnroll; ++u) {
@@ -580,7 +673,7 @@ loss_rows_kernel(const LayerTab t, const GradTab g, const LossParams p,
 #pragma unroll
   for (int k = 0; k < 4; ++k) s_red[threadIdx.x][k] = r[k];
   __syncthreads();
-  for (int o = kRowThreads / 2; o > 0; o >>= 1) {
+  for (int o = kFinishThreads / 2; o > 0; o >>= 1) {
     if (threadIdx.x < o) {
 #pragma unroll
       for (int k = 0; k < 4; ++k) s_red[threadIdx.x][k] += s_red[threadIdx.x + o][k];
@@ -607,7 +700,6 @@ loss_rows_kernel(const LayerTab t, const GradTab g, const LossParams p,
     losses4[1] = iou_l;
     losses4[2] = cls_l;
     losses4[3] = obj_l;
-    *ticket = 0u;  // ready for the next call on this stream
   }
 }
 
@@ -615,25 +707,32 @@ loss_rows_kernel(const LayerTab t, const GradTab g, const LossParams p,
 
 namespace yh {
 
-enum { kPhaseDense = 1, kPhaseRows = 2 };
+enum { kPhaseDense = 1, kPhaseRows = 2, kPhaseFinish = 4 };
 
-// Both phases of YoloLoss::forward+backward.  kPhaseDense needs only the heads (it can run
-// concurrently with yh_assign on another stream); kPhaseRows must be ordered after BOTH the
-// dense phase of the same workspace (it overwrites the objectness gradient of the matched
-// cells and folds the dense partial sums into the losses) and yh_assign.
+// The three phases of YoloLoss::forward+backward.
+//   kPhaseDense   needs only the heads;
+//   kPhaseRows    needs the heads and the matches (yh_assign); stages the row gradients in the
+//                 workspace, so it may run concurrently with kPhaseDense on another stream;
+//   kPhaseFinish  ordered after both: scatters the staged rows over the dense gradient and
+//                 reduces the partial sums into losses4.
 static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
                        const YhLayer* layers, int L, int B, int C, const int64_t* m_batch,
                        const int64_t* m_flat, const float* m_target, const int64_t* m_class,
                        const int32_t* M_dev, int capacity, const YhLossCfg* cfg,
                        float* losses4_dev, float* iou_score_dev, float* pred_rows_dev,
-                       float* const* grad_heads, void* stream) {
+                       float* const* grad_heads, int want_grad_rows, void* stream) {
   YH_REQUIRE(ws != nullptr, "workspace is NULL");
   YH_REQUIRE(cfg != nullptr, "NULL argument");
   if (phases & kPhaseRows) {
-    YH_REQUIRE(losses4_dev != nullptr && M_dev != nullptr, "NULL argument");
+    YH_REQUIRE(M_dev != nullptr, "NULL argument");
     YH_REQUIRE(capacity == 0 || (m_batch && m_flat && m_target && m_class), "match list is NULL");
     YH_REQUIRE(((uintptr_t)m_target & 15) == 0, "m_target not 16-byte aligned");
   }
+  if (phases & kPhaseFinish) {
+    YH_REQUIRE(losses4_dev != nullptr && M_dev != nullptr, "NULL argument");
+    YH_REQUIRE(capacity == 0 || (m_batch && m_flat), "match list is NULL");
+  }
+  YH_REQUIRE(capacity >= 0, "capacity=%d", capacity);
   YH_REQUIRE(B >= 1 && B <= ws->max_batch, "B=%d outside 1..max_batch=%d", B, ws->max_batch);
   LayerTab tab;
   int rc = build_layer_tab(layers, L, C, heads, &tab);
@@ -649,11 +748,7 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
              "classification_loss_weight must be non-negative");
   YH_REQUIRE(cfg->reduction == YH_REDUCTION_MEAN || cfg->reduction == YH_REDUCTION_SUM,
              "reduction %d is not supported", cfg->reduction);
-  if (cfg->box_metric == YH_METRIC_HAUSDORFF) {
-    set_error("box_metric Hausdorff is outside the accelerated path (DESIGN.md, out of scope)");
-    return YH_ERR_UNSUPPORTED;
-  }
-  YH_REQUIRE(cfg->box_metric >= YH_METRIC_IOU && cfg->box_metric <= YH_METRIC_CIOU,
+  YH_REQUIRE(cfg->box_metric >= YH_METRIC_IOU && cfg->box_metric <= YH_METRIC_HAUSDORFF,
              "box_metric=%d", cfg->box_metric);
 
   GradTab g;
@@ -662,7 +757,7 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
     for (int l = 0; l < L; ++l) {
       YH_REQUIRE(grad_heads[l] != nullptr, "grad_heads[%d] is NULL", l);
       YH_REQUIRE(((uintptr_t)grad_heads[l] & 15) == 0, "grad_heads[%d] not 16-byte aligned", l);
-      YH_REQUIRE(((uintptr_t)heads[l] & 15) == 0, "heads[%d] not 16-byte aligned", l);
+      YH_REQUIRE(!heads || ((uintptr_t)heads[l] & 15) == 0, "heads[%d] not 16-byte aligned", l);
       g.grad[l] = grad_heads[l];
     }
   }
@@ -686,7 +781,12 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
   const float numel = (float)((long long)B * tab.N);
   // 16 CTAs per SM (two waves of 8 resident): measured best on B200 both alone (88 us vs 94 us
   // at 2..8 CTAs/SM) and inside the overlapped step (profiles/README.md, sweep r1c)
-  int dense_grid = ws->num_sms * 16;
+  static const int dense_cps = []() {  // tuning knob for sweeps (profiles/README.md)
+    const char* e = getenv("YH_DENSE_CTAS_PER_SM");
+    const int v = e ? atoi(e) : 0;
+    return v > 0 ? v : 16;
+  }();
+  int dense_grid = ws->num_sms * dense_cps;
   if (dense_grid > kPartHalf) dense_grid = kPartHalf;
   if (!(phases & kPhaseDense)) {
   } else if (grad_heads) {
@@ -699,19 +799,37 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
         tab, g, B, numel, p.w_obj, p.reduction, ws->partials);
   }
   if (phases & kPhaseDense) YH_LAUNCHED(s);
-  if (!(phases & kPhaseRows)) return YH_OK;
   int row_grid = ws->num_sms * 4;  // resident in one wave; rows beyond that grid-stride
   const int rows_per_cta = (kRowThreads / 32) * kRowsPerWarp;
   const int need = (capacity + rows_per_cta - 1) / rows_per_cta;
   if (row_grid > need) row_grid = need;
   if (row_grid < 1) row_grid = 1;
   if (row_grid > kPartHalf) row_grid = kPartHalf;
-  YH_TIME(YH_K_LOSS_ROWS, s);
-  loss_rows_kernel<<<row_grid, kRowThreads, 0, s>>>(
-      tab, g, p, (const long long*)m_batch, (const long long*)m_flat, m_target,
-      (const long long*)m_class, M_dev, capacity, iou_score_dev, pred_rows_dev, ws->partials,
-      dense_grid, ws->ticket, losses4_dev);
-  YH_LAUNCHED(s);
+  const bool want_grad = grad_heads != nullptr || want_grad_rows != 0;
+  if (want_grad && (phases & (kPhaseRows | kPhaseFinish)) && capacity > 0) {
+    rc = reserve_rows(ws, (size_t)capacity * (size_t)tab.E, s);
+    if (rc) return rc;
+  }
+  if (phases & kPhaseRows) {
+    YH_TIME(YH_K_LOSS_ROWS, s);
+    loss_rows_kernel<<<row_grid, kRowThreads, 0, s>>>(
+        tab, p, (const long long*)m_batch, (const long long*)m_flat, m_target,
+        (const long long*)m_class, M_dev, capacity, iou_score_dev, pred_rows_dev,
+        want_grad ? ws->row_grad : nullptr, ws->partials);
+    YH_LAUNCHED(s);
+  }
+  if (phases & kPhaseFinish) {
+    int fin_grid = 1;
+    if (grad_heads && capacity > 0) {
+      fin_grid = (capacity + kFinishThreads / 32 - 1) / (kFinishThreads / 32);
+      if (fin_grid > ws->num_sms * 8) fin_grid = ws->num_sms * 8;
+    }
+    YH_TIME(YH_K_LOSS_FINISH, s);
+    loss_finish_kernel<<<fin_grid, kFinishThreads, 0, s>>>(
+        tab, g, p, (const long long*)m_batch, (const long long*)m_flat, M_dev, capacity,
+        grad_heads ? ws->row_grad : nullptr, ws->partials, dense_grid, row_grid, losses4_dev);
+    YH_LAUNCHED(s);
+  }
   return YH_OK;
 }
 
@@ -724,15 +842,18 @@ int yh_loss_fwd_bwd(YhWorkspace* ws, const float* const* heads, const YhLayer* l
                     const float* m_target, const int64_t* m_class, const int32_t* M_dev,
                     int capacity, const YhLossCfg* cfg, float* losses4_dev, float* iou_score_dev,
                     float* pred_rows_dev, float* const* grad_heads, void* stream) {
-  return yh::loss_phases(yh::kPhaseDense | yh::kPhaseRows, ws, heads, layers, L, B, C, m_batch,
-                         m_flat, m_target, m_class, M_dev, capacity, cfg, losses4_dev,
-                         iou_score_dev, pred_rows_dev, grad_heads, stream);
+  YH_REQUIRE(heads != nullptr, "heads is NULL");
+  return yh::loss_phases(yh::kPhaseDense | yh::kPhaseRows | yh::kPhaseFinish, ws, heads, layers, L,
+                         B, C, m_batch, m_flat, m_target, m_class, M_dev, capacity, cfg,
+                         losses4_dev, iou_score_dev, pred_rows_dev, grad_heads, 0, stream);
 }
 
 int yh_loss_dense(YhWorkspace* ws, const float* const* heads, const YhLayer* layers, int L, int B,
                   int C, const YhLossCfg* cfg, float* const* grad_heads, void* stream) {
+  YH_REQUIRE(heads != nullptr, "heads is NULL");
   return yh::loss_phases(yh::kPhaseDense, ws, heads, layers, L, B, C, nullptr, nullptr, nullptr,
-                         nullptr, nullptr, 0, cfg, nullptr, nullptr, nullptr, grad_heads, stream);
+                         nullptr, nullptr, 0, cfg, nullptr, nullptr, nullptr, grad_heads, 0,
+                         stream);
 }
 
 int yh_loss_rows(YhWorkspace* ws, const float* const* heads, const YhLayer* layers, int L, int B,
@@ -740,9 +861,30 @@ int yh_loss_rows(YhWorkspace* ws, const float* const* heads, const YhLayer* laye
                  const int64_t* m_class, const int32_t* M_dev, int capacity, const YhLossCfg* cfg,
                  float* losses4_dev, float* iou_score_dev, float* pred_rows_dev,
                  float* const* grad_heads, void* stream) {
+  YH_REQUIRE(heads != nullptr, "heads is NULL");
+  return yh::loss_phases(yh::kPhaseRows | yh::kPhaseFinish, ws, heads, layers, L, B, C, m_batch,
+                         m_flat, m_target, m_class, M_dev, capacity, cfg, losses4_dev,
+                         iou_score_dev, pred_rows_dev, grad_heads, 0, stream);
+}
+
+int yh_loss_rows_compute(YhWorkspace* ws, const float* const* heads, const YhLayer* layers, int L,
+                         int B, int C, const int64_t* m_batch, const int64_t* m_flat,
+                         const float* m_target, const int64_t* m_class, const int32_t* M_dev,
+                         int capacity, const YhLossCfg* cfg, float* iou_score_dev,
+                         float* pred_rows_dev, int want_grad, void* stream) {
+  YH_REQUIRE(heads != nullptr, "heads is NULL");
   return yh::loss_phases(yh::kPhaseRows, ws, heads, layers, L, B, C, m_batch, m_flat, m_target,
-                         m_class, M_dev, capacity, cfg, losses4_dev, iou_score_dev, pred_rows_dev,
-                         grad_heads, stream);
+                         m_class, M_dev, capacity, cfg, nullptr, iou_score_dev, pred_rows_dev,
+                         nullptr, want_grad, stream);
+}
+
+int yh_loss_finish(YhWorkspace* ws, const YhLayer* layers, int L, int B, int C,
+                   const int64_t* m_batch, const int64_t* m_flat, const int32_t* M_dev,
+                   int capacity, const YhLossCfg* cfg, float* losses4_dev,
+                   float* const* grad_heads, void* stream) {
+  return yh::loss_phases(yh::kPhaseFinish, ws, nullptr, layers, L, B, C, m_batch, m_flat, nullptr,
+                         nullptr, M_dev, capacity, cfg, losses4_dev, nullptr, nullptr, grad_heads,
+                         0, stream);
 }
 
 }  // extern "C"

@@ -229,7 +229,9 @@ class YoloLoss:
             total.grad_fn.saved_grads = [g if h.requires_grad else None
                                          for g, h in zip(grads, prediction.heads)]
         out = YoloLossOutput(total, losses4[1], losses4[2], losses4[3])
+        # BoxMetric::Hausdorff yields no score (loss_.rs:285-288)
+        haus = self.init.box_metric.lower() == "hausdorff"
         aux = YoloLossAuxiliary(_matching_output(prediction, a, M, pred_rows),
-                                iou_score[:M].view(-1, 1))
+                                None if haus else iou_score[:M].view(-1, 1))
         self.last_grads = grads
         return out, aux

@@ -60,6 +60,8 @@ class DeviceStep:
         self.conf = torch.empty(self.kcap, dtype=f32, device=device)
         self.K = torch.zeros(1, dtype=i32, device=device)
         self._grad_ptrs = _lib.ptr_array(self.grads) if with_grad else None
+        # staging of the matched-row gradients: reserved now, graphs cannot allocate
+        _lib.check(self.lib.yh_workspace_reserve_rows(self.ws.handle, self.mcap, self.C))
         self._side = None
         self._graph = None
         self.kernels_in_graph = 0
@@ -69,11 +71,11 @@ class DeviceStep:
         n = self.N * self.B
         return {"decode_kernel": 32 * n, "loss_dense_kernel": 344 * n, "nms_filter_kernel": 340 * n}
 
-    KERNELS_PER_STEP = 8
+    KERNELS_PER_STEP = 9
 
     def run(self, heads: Sequence[torch.Tensor], gt_dev: torch.Tensor, off_dev: torch.Tensor, stream=None):
         """heads: L contiguous f32 CUDA tensors [B, A*(5+C), H, W]; gt_dev [G,5] f64; off_dev [B+1] i32.
-        Enqueues 8 kernels on ONE stream, in the order the reference executes them; nothing
+        Enqueues 9 kernels on ONE stream, in the order the reference executes them; nothing
         synchronises."""
         s = stream if stream is not None else torch.cuda.current_stream(self.dev).cuda_stream
         self._decode(_lib.ptr_array(heads), s)
@@ -105,16 +107,19 @@ class DeviceStep:
                                    self.ki.data_ptr(), self.tlbr.data_ptr(), self.conf.data_ptr(),
                                    self.K.data_ptr(), self.kcap, s))
 
-    # -- the same 8 kernels as a fork/join over four streams --------------------------------
+    # -- the same 9 kernels as a fork/join over four streams --------------------------------
     def run_overlapped(self, heads, gt_dev, off_dev):
         """The step as the dependency graph it really is (the reference runs it as one sequence,
         train/src/train/single_gpu.rs:152-186):
 
-            decode                                   (Detect2D x L + merge)
-            assign ----------------\
-            loss_dense -------------+--> loss_rows   (YoloLoss fwd+bwd; the dense objectness pass
-            nms_filter -> nms_segment -> nms_emit     needs no matches)
+            decode                                            (Detect2D x L + merge)
+            assign -> loss_rows (staged row gradients) --\
+            loss_dense ----------------------------------+--> loss_finish (scatter + reduce)
+            nms_filter -> nms_segment -> nms_emit
 
+        (YoloLoss fwd+bwd: neither the dense objectness pass nor the matched rows need each
+        other; only the few-microsecond scatter of the staged row gradients over the dense
+        gradient is ordered after both.)
         The four branches are forked from the current stream onto side streams and joined back
         into it, so the latency-bound kernels (one CTA per image: assignment, greedy NMS) run
         under the HBM-bound ones (decode, dense loss, candidate filter).  Capturable in a CUDA
@@ -135,6 +140,11 @@ class DeviceStep:
         _lib.check(self.lib.yh_loss_dense(self.ws.handle, hp, self.layers, self.L, self.B, self.C, self.cfg,
                                           self._grad_ptrs, main.cuda_stream))
         self._assign(gt_dev, off_dev, s_asg.cuda_stream)
+        _lib.check(self.lib.yh_loss_rows_compute(
+            self.ws.handle, hp, self.layers, self.L, self.B, self.C, self.m_batch.data_ptr(),
+            self.m_flat.data_ptr(), self.m_target.data_ptr(), self.m_class.data_ptr(),
+            self.M.data_ptr(), self.mcap, self.cfg, self.iou_score.data_ptr(),
+            self.pred_rows.data_ptr(), 1 if self._grad_ptrs is not None else 0, s_asg.cuda_stream))
         self._nms(hp, s_nms.cuda_stream)
         self._decode(hp, s_dec.cuda_stream)
         joins = []
@@ -143,7 +153,10 @@ class DeviceStep:
             e.record(st)
             joins.append(e)
         main.wait_event(joins[1])
-        self._loss(self.lib.yh_loss_rows, hp, main.cuda_stream)
+        _lib.check(self.lib.yh_loss_finish(
+            self.ws.handle, self.layers, self.L, self.B, self.C, self.m_batch.data_ptr(),
+            self.m_flat.data_ptr(), self.M.data_ptr(), self.mcap, self.cfg, self.losses4.data_ptr(),
+            self._grad_ptrs, main.cuda_stream))
         main.wait_event(joins[0])
         main.wait_event(joins[2])
 
