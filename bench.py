@@ -39,7 +39,7 @@ def parse():
     p.add_argument("--warmup", type=int, default=10)
     p.add_argument("--impl", default="native", choices=["native", "reference"])
     p.add_argument("--batch", type=int, default=64, help="images per GPU")
-    p.add_argument("--cpu-sample", type=int, default=8, help="images per CPU-baseline sample")
+    p.add_argument("--cpu-sample", type=int, default=64, help="images per CPU-baseline pass")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
     return p.parse_args()
@@ -277,6 +277,22 @@ def run_native(args):
                                       "achieved_GBps": (alg[n] / (kern_ms[n] * 1e-3) / 1e9) if n in alg else None}
                                   for n in kern_ms if n != dom}}
 
+    # whole-step view: SURVEY.md §8d algorithmic bytes of everything the step does (decode 32·N,
+    # loss fwd+bwd 344·N + 340·M, filter 4·N objectness plane + 32-byte sectors of the C class
+    # logits of the P instances that pass the objectness test, NMS 32·K) over the step time
+    n_inst = step.N * B
+    obj_pass = 0
+    for h, (H, W_) in zip(heads, spec.shapes):
+        o = h.view(B, 5 + spec.num_classes, -1, H, W_)[:, 4]
+        obj_pass += int((torch.sigmoid(o) >= NMS_CONF).sum())
+    step_bytes = 32 * n_inst + 344 * n_inst + 340 * M + 4 * n_inst + 32 * spec.num_classes * obj_pass + 32 * Kdet
+    roofline["step"] = {"algorithmic_bytes": step_bytes, "achieved": step_bytes / (ms / K * 1e-3) / 1e9,
+                        "frac": step_bytes / (ms / K * 1e-3) / 1e9 / peak, "unit": "GB/s",
+                        "objectness_passing_instances": obj_pass,
+                        "note": "all kernels of the step over the step time; the random 32-byte sector "
+                                "reads/writes of the matched rows and of the NMS candidates cost about "
+                                "twice their byte count in DRAM time (profiles/README.md)"}
+
     # end to end through host buffers (pinned): every step pays H2D of its heads+labels, the 8
     # kernels, and D2H of losses + matches + detections + head gradients.  HostPipeline overlaps
     # step i's compute with step i+1's H2D and step i-1's D2H (2 slots, 3 streams); HostStep (one
@@ -344,9 +360,9 @@ def run_native(args):
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        v, per, cores = time_cpu_reference(args.cpu_sample, 2, 1)
+        v, per, cores = time_cpu_reference(args.cpu_sample, 20, 1)
         cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
-               "sample": f"{args.cpu_sample} images of the same workload, 2 timed passes after 1 warm-up "
+               "sample": f"{args.cpu_sample} images of the same workload, 20 timed passes after 1 warm-up "
                          f"({per:.2f} s/pass)"}
 
     if rank == 0:

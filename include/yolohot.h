@@ -58,6 +58,17 @@ typedef enum YhBoxMetric {
  * not part of the scalar-loss ABI). */
 typedef enum YhReduction { YH_REDUCTION_MEAN = 0, YH_REDUCTION_SUM = 1 } YhReduction;
 
+/* `ObjectnessLossKind` / `ClassificationLossKind` (`loss_.rs:191-205`): BceWithLogitsLoss
+ * (`bce_with_logits_loss.rs:60-85`), FocalLoss wrapping it (`focal_loss.rs:66-108`), L2Loss = mse on
+ * the LOGITS (`l2_loss.rs:13-15`), CrossEntropyLoss with the dense target's arg-max
+ * (`cross_entropy.rs:19-58`, classification only). */
+typedef enum YhLossKind {
+  YH_LOSS_BCE = 0,
+  YH_LOSS_FOCAL = 1,
+  YH_LOSS_L2 = 2,
+  YH_LOSS_CROSS_ENTROPY = 3
+} YhLossKind;
+
 /* One detection layer = one `DetectionInfo` (`merged_dense_detection.rs:497-507`)
  * plus what `Detect2D` holds (`detect_2d.rs:33-39`). Anchors are RATIO units (h, w)
  * in f64 exactly as the reference stores them (`Ratio<HW<R64>>`); the decode casts
@@ -82,6 +93,10 @@ typedef struct YhLossCfg {
   int32_t has_objectness_pos_weight; /* 0 */
   int32_t _pad;
   double objectness_pos_weight;
+  int32_t objectness_loss_kind;      /* YhLossKind: Bce (default), Focal, L2        (loss_.rs:115-145) */
+  int32_t classification_loss_kind;  /* YhLossKind: Bce (default), Focal, L2, CrossEntropy (:89-113) */
+  double focal_loss_gamma;           /* 0.0 (YoloLossInit default, loss_.rs:176); alpha is FocalLossInit's
+                                        fixed 0.25 (`tch-modules/src/focal_loss.rs:27-34`) */
 } YhLossCfg;
 
 typedef struct YhWorkspace YhWorkspace;

@@ -28,6 +28,9 @@ class LossConfig:
     objectness_pos_weight: Optional[float] = None
     match_rect4: bool = True
     anchor_scale_thresh: float = 4.0
+    focal_loss_gamma: float = 0.0             # loss_.rs:176
+    objectness_loss_kind: str = "bce"         # bce | focal | l2            (loss_.rs:115-145)
+    classification_loss_kind: str = "bce"     # bce | focal | l2 | crossentropy (loss_.rs:89-113)
 
 
 def _bce(inp, target, pos_weight, reduction):
@@ -36,6 +39,52 @@ def _bce(inp, target, pos_weight, reduction):
         return torch.zeros((), dtype=torch.float32, device=inp.device)
     return F.binary_cross_entropy_with_logits(inp, target, weight=None, pos_weight=pos_weight,
                                               reduction=reduction)
+
+
+def _reduce(loss, reduction):
+    return loss.mean() if reduction == "mean" else loss.sum()
+
+
+def _focal(inp, target, pos_weight, gamma, reduction, alpha=0.25):
+    """FocalLoss::forward (tch-modules/src/focal_loss.rs:66-108) around BceWithLogitsLoss with
+    Reduction::None (loss_.rs:97-111,127-143); alpha = FocalLossInit::default's 0.25."""
+    if inp.numel() == 0 and reduction == "mean":
+        return torch.zeros((), dtype=torch.float32, device=inp.device)
+    orig_loss = _bce(inp, target, pos_weight, "none")
+    input_prob = inp.sigmoid()
+    p_t = target * input_prob + (1.0 - target) * (1.0 - input_prob)
+    alpha_factor = target * alpha + (1.0 - target) * (1.0 - alpha)
+    modulating_factor = (-p_t + 1.0).pow(torch.tensor(gamma, dtype=torch.float64))
+    loss = orig_loss * alpha_factor * modulating_factor
+    return loss if reduction == "none" else _reduce(loss, reduction)
+
+
+def _l2(inp, target, reduction):
+    """L2Loss::forward (tch-modules/src/l2_loss.rs:13-15): mse_loss on the logits."""
+    return F.mse_loss(inp, target, reduction=reduction)
+
+
+def _cross_entropy(inp, target_dense, reduction):
+    """CrossEntropyLoss::new(false, ..)::forward (tch-modules/src/cross_entropy.rs:19-58): arg-max of
+    the dense target, then cross_entropy_for_logits = log_softmax + nll per row."""
+    sparse = target_dense.max(dim=1)[1]
+    if inp.numel() == 0 and reduction == "mean":
+        return torch.zeros((), dtype=torch.float32, device=inp.device)
+    loss = F.nll_loss(F.log_softmax(inp, dim=-1), sparse, reduction="none")
+    return _reduce(loss, reduction)
+
+
+def _kind_loss(kind, inp, target, pos_weight, gamma, reduction):
+    kind = kind.lower()
+    if kind == "bce":
+        return _bce(inp, target, pos_weight, reduction)
+    if kind == "focal":
+        return _focal(inp, target, pos_weight, gamma, reduction)
+    if kind == "l2":
+        return _l2(inp, target, reduction)
+    if kind == "crossentropy":
+        return _cross_entropy(inp, target, reduction)
+    raise ValueError(kind)
 
 
 def yolo_loss_from_matches(merged: dict, batches, flats, target_cycxhw, target_class,
@@ -69,7 +118,8 @@ def yolo_loss_from_matches(merged: dict, batches, flats, target_cycxhw, target_c
         sparse = target_class.view(-1, 1)
         pos_values = torch.full(sparse.shape, pos, dtype=torch.float32, device=dev)
         target_dense = torch.full_like(pred_class, neg).scatter_(1, sparse, pos_values)
-    cls_loss = _bce(pred_class, target_dense, None, cfg.reduction)
+    cls_loss = _kind_loss(cfg.classification_loss_kind, pred_class, target_dense, None,
+                          cfg.focal_loss_gamma, cfg.reduction)
 
     # objectness_loss (:376-468)
     pred_obj = merged["obj_logit"]
@@ -84,7 +134,8 @@ def yolo_loss_from_matches(merged: dict, batches, flats, target_cycxhw, target_c
     pw = None
     if cfg.objectness_pos_weight is not None:
         pw = torch.tensor([cfg.objectness_pos_weight], dtype=torch.float32, device=dev)
-    obj_loss = _bce(pred_obj.view(B, -1), target_obj.view(B, -1), pw, cfg.reduction)
+    obj_loss = _kind_loss(cfg.objectness_loss_kind, pred_obj.view(B, -1), target_obj.view(B, -1), pw,
+                          cfg.focal_loss_gamma, cfg.reduction)
 
     total = (cfg.iou_loss_weight * iou_loss + cfg.classification_loss_weight * cls_loss
              + cfg.objectness_loss_weight * obj_loss)  # (:258-260)

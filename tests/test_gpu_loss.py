@@ -27,7 +27,9 @@ def _run(dev, spec, B, targets, seed=3, **kw):
         smooth_classification_coef=init.smooth_classification_coef,
         smooth_objectness_coef=init.smooth_objectness_coef,
         objectness_pos_weight=init.objectness_pos_weight,
-        match_rect4=init.match_grid_method == "Rect4", anchor_scale_thresh=init.anchor_scale_thresh)
+        match_rect4=init.match_grid_method == "Rect4", anchor_scale_thresh=init.anchor_scale_thresh,
+        focal_loss_gamma=init.focal_loss_gamma, objectness_loss_kind=init.objectness_loss_kind.lower(),
+        classification_loss_kind=init.classification_loss_kind.lower())
     ref = oloss.yolo_loss(heads_cpu, infos, spec.num_classes, targets, cfg, use_c_matcher=True)
     return heads, out, aux, ref
 
@@ -78,6 +80,32 @@ def test_loss_hausdorff_yolov4_608_and_no_score(dev):
                                 smooth_objectness_coef=0.2)
     assert aux.iou_score is None
     _compare(heads, out, aux, ref, "hausdorff 608")
+
+
+@pytest.mark.parametrize("kw", [
+    dict(objectness_loss_kind="Focal", classification_loss_kind="Focal"),                       # gamma 0 default
+    dict(objectness_loss_kind="Focal", classification_loss_kind="Focal", focal_loss_gamma=1.5),
+    dict(objectness_loss_kind="Focal", focal_loss_gamma=2.0, objectness_pos_weight=1.7,
+         smooth_objectness_coef=0.4, box_metric="ciou"),
+    dict(objectness_loss_kind="L2", classification_loss_kind="L2"),
+    dict(classification_loss_kind="CrossEntropy"),
+    dict(classification_loss_kind="CrossEntropy", reduction="sum", objectness_loss_kind="L2"),
+    dict(classification_loss_kind="CrossEntropy", smooth_classification_coef=1.0),            # pos == neg: arg-max is 0
+], ids=lambda kw: ",".join(f"{k}={v}" for k, v in kw.items()))
+def test_loss_kinds_small(dev, kw):
+    """ObjectnessLossKind / ClassificationLossKind (loss_.rs:89-145): Focal, L2, CrossEntropy."""
+    spec = synth.small_spec()
+    targets = synth.make_targets(spec, 3, 43, n_max=7, clustered=0.3)
+    heads, out, aux, ref = _run(dev, spec, 3, targets, **kw)
+    _compare(heads, out, aux, ref, str(kw))
+
+
+def test_loss_kinds_yolov4_608(dev):
+    spec = synth.yolov4_608()
+    targets = synth.make_targets(spec, 4, 23)
+    heads, out, aux, ref = _run(dev, spec, 4, targets, box_metric="ciou", objectness_loss_kind="Focal",
+                                classification_loss_kind="CrossEntropy", focal_loss_gamma=1.5)
+    _compare(heads, out, aux, ref, "608 focal+ce")
 
 
 def test_loss_options_sum_smoothing_posweight(dev):

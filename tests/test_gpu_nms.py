@@ -117,6 +117,19 @@ def test_nms_by_scores_matches_torchvision(dev):
     assert np.array_equal(got.cpu().numpy(), ref)
 
 
+@pytest.mark.parametrize("K,groups", [(100000, 80), (200000, 80), (100000, 4)])
+def test_nms_sweep_100k_200k(dev, K, groups):
+    """BASELINE config 4, the sizes above one 65 536-row chunk: one global NMS over all rows,
+    checked against torchvision's batched_nms (C++ on the host; the numpy oracle is O(K*kept))."""
+    import torchvision
+    ltrb, scores, grp = synth.make_nms_boxes(K, 7 + K + groups, num_groups=groups, dup_frac=0.0)
+    ref = torchvision.ops.batched_nms(torch.from_numpy(ltrb), torch.from_numpy(scores),
+                                      torch.from_numpy(grp), 0.5).numpy()
+    got = yh.nms_by_scores(torch.from_numpy(ltrb).to(dev), torch.from_numpy(scores).to(dev),
+                           torch.from_numpy(grp).to(dev), 0.5)
+    assert np.array_equal(got.cpu().numpy(), ref)
+
+
 def test_nms_by_scores_degenerate_boxes(dev):
     """zero-area and identical boxes, negative scores, NaN IoU (0/0 is not > thr)."""
     ltrb = np.array([[0, 0, 0, 0], [0, 0, 0, 0], [0.1, 0.1, 0.5, 0.5], [0.1, 0.1, 0.5, 0.5],

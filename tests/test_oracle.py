@@ -248,3 +248,25 @@ def test_hausdorff_known_answers():
         for i, j in ((0, 1), (0, 3), (2, 1), (2, 3)):
             best = np.maximum(best, c[i] ** 2 + c[j] ** 2)
     assert np.allclose(got, np.sqrt(best), rtol=1e-5, atol=1e-6)
+
+
+def test_loss_kinds_closed_forms():
+    """Focal / L2 / CrossEntropy restatements (tch-modules focal_loss.rs:66-108, l2_loss.rs:13-15,
+    cross_entropy.rs:19-58) against closed forms."""
+    g = torch.Generator().manual_seed(11)
+    x = torch.randn(6, 9, generator=g)
+    t = torch.rand(6, 9, generator=g)
+    bce = torch.nn.functional.binary_cross_entropy_with_logits(x, t, reduction="none")
+    # gamma = 0 (YoloLossInit default): focal = bce * alpha_factor
+    assert torch.allclose(oloss._focal(x, t, None, 0.0, "mean"), (bce * (t * 0.25 + (1 - t) * 0.75)).mean())
+    p = torch.sigmoid(x)
+    pt = t * p + (1 - t) * (1 - p)
+    want = (bce * (t * 0.25 + (1 - t) * 0.75) * (1 - pt) ** 1.5).sum()
+    assert torch.allclose(oloss._focal(x, t, None, 1.5, "sum"), want, rtol=1e-5)
+    assert torch.allclose(oloss._l2(x, t, "mean"), ((x - t) ** 2).mean())
+    assert torch.allclose(oloss._cross_entropy(x, t, "mean"),
+                          torch.nn.functional.cross_entropy(x, t.argmax(1)))
+    # empty input with mean reduction gives 0 (focal_loss.rs:79-81, cross_entropy.rs:45-47)
+    e = torch.zeros(0, 9)
+    assert float(oloss._focal(e, e, None, 1.5, "mean")) == 0.0
+    assert float(oloss._cross_entropy(e, e, "mean")) == 0.0

@@ -14,6 +14,7 @@ YH_OK, YH_ERR_INVALID, YH_ERR_CUDA, YH_ERR_CAPACITY, YH_ERR_UNSUPPORTED = range(
 
 METRICS = {"iou": 0, "giou": 1, "diou": 2, "ciou": 3, "hausdorff": 4}
 REDUCTIONS = {"mean": 0, "sum": 1}
+LOSS_KINDS = {"bce": 0, "focal": 1, "l2": 2, "crossentropy": 3}
 
 
 class YhLayer(ctypes.Structure):
@@ -27,7 +28,9 @@ class YhLossCfg(ctypes.Structure):
                 ("iou_loss_weight", c_double), ("classification_loss_weight", c_double),
                 ("objectness_loss_weight", c_double), ("smooth_classification_coef", c_double),
                 ("smooth_objectness_coef", c_double), ("has_objectness_pos_weight", c_int32),
-                ("_pad", c_int32), ("objectness_pos_weight", c_double)]
+                ("_pad", c_int32), ("objectness_pos_weight", c_double),
+                ("objectness_loss_kind", c_int32), ("classification_loss_kind", c_int32),
+                ("focal_loss_gamma", c_double)]
 
 
 class YoloHotError(RuntimeError):

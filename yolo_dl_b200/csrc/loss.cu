@@ -45,11 +45,52 @@ struct LossParams {
   float obj_base, obj_coef; // 1-s_o, s_o (loss_.rs:397-406)
   int has_pw;
   float pw;
+  int obj_kind, cls_kind;   // YhLossKind
+  float gamma;              // focal_loss_gamma
 };
 
 __device__ __forceinline__ float softplus_f(float x) {
   // log(1 + exp(x)) = max(x,0) + log1p(exp(-|x|))
   return fmaxf(x, 0.0f) + log1pf(expf(-fabsf(x)));
+}
+
+__device__ __forceinline__ float sigmoid_l(float x) { return 1.0f / (1.0f + expf(-x)); }
+
+// The non-default loss kinds, per logit: loss(x, t) and d loss / d x.
+//   L2     mse on the logit (l2_loss.rs:13-15): (x-t)^2
+//   Focal  (focal_loss.rs:90-98) around BceWithLogits (reduction None, optional pos_weight):
+//          bce * (t*a + (1-t)*(1-a)) * (1 - p_t)^gamma,  p_t = t*p + (1-t)*(1-p),  a = 0.25;
+//          reverse mode of the same chain; pow(., 0) has a zero derivative like ATen's.
+__device__ __forceinline__ float kind_loss(const int kind, const float x, const float t,
+                                           const bool has_pw, const float pw, const float gamma,
+                                           float& dx) {
+  if (kind == YH_LOSS_L2) {
+    const float d = x - t;
+    dx = 2.0f * d;
+    return d * d;
+  }
+  const float kAlpha = 0.25f;  // FocalLossInit::default (focal_loss.rs:27-34)
+  const float lw = has_pw ? (pw - 1.0f) * t + 1.0f : 1.0f;
+  const float b = (1.0f - t) * x + lw * softplus_f(-x);
+  const float p = sigmoid_l(x);
+  float db;
+  if (has_pw) {
+    const float tp = pw * t;
+    db = ((tp + 1.0f) - t) * p - tp;
+  } else {
+    db = p - t;
+  }
+  const float pt = t * p + (1.0f - t) * (1.0f - p);
+  const float af = t * kAlpha + (1.0f - t) * (1.0f - kAlpha);
+  const float q = -pt + 1.0f;
+  float mf = 1.0f, dmf = 0.0f;
+  if (gamma != 0.0f) {
+    mf = powf(q, gamma);
+    const float dpt = (t - (1.0f - t)) * ((1.0f - p) * p);
+    dmf = -(gamma * powf(q, gamma - 1.0f)) * dpt;
+  }
+  dx = (db * mf + b * dmf) * af;
+  return (b * af) * mf;
 }
 
 // ---------------------------------------------------------------------------------
@@ -70,10 +111,12 @@ constexpr int kTileUnroll = 8;
 constexpr int kTileQuads = kDenseThreads * kTileUnroll;  // 2048 quads = 8192 floats = 32 KB
 constexpr int kTileFloats = kTileQuads * 4;
 
-template <bool GRAD>
+// BCE: the default objectness kind keeps its own instantiation (40 registers, 6 CTAs/SM)
+template <bool GRAD, bool BCE>
 __global__ void __launch_bounds__(kDenseThreads)
 loss_dense_kernel(const LayerTab t, const GradTab g, const int B, const float numel,
-                  const float w_obj, const int reduction, double* __restrict__ partials) {
+                  const float w_obj, const int reduction, const int kind, const float gamma,
+                  double* __restrict__ partials) {
   double acc = 0.0;
   if (GRAD) {
     // ---- pass 1: the quads that hold at least one objectness element ---------------------
@@ -120,9 +163,14 @@ loss_dense_kernel(const LayerTab t, const GradTab g, const int B, const float nu
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
           if (idx + k >= o0 && idx + k < o1) {
-            acc += (double)softplus_f(x[k]);
-            // BCE backward, target 0: sigmoid(x) [/numel for Mean] * upstream w_obj
-            float gi = sigmoid_f(x[k]);
+            float gi;
+            if (BCE) {
+              acc += (double)softplus_f(x[k]);
+              // BCE backward, target 0: sigmoid(x) [/numel for Mean] * upstream w_obj
+              gi = sigmoid_f(x[k]);
+            } else {
+              acc += (double)kind_loss(kind, x[k], 0.0f, false, 0.0f, gamma, gi);
+            }
             if (reduction == YH_REDUCTION_MEAN) gi = gi / numel;
             v[k] = gi * w_obj;
           }
@@ -220,7 +268,9 @@ loss_dense_kernel(const LayerTab t, const GradTab g, const int B, const float nu
       const long long b = li / run;
       const long long j = li - b * run;
       const float x = __ldcs(t.head[l] + b * per_img + 4LL * run + j);
-      acc += (double)softplus_f(x);
+      float unused;
+      acc += BCE ? (double)softplus_f(x)
+                                   : (double)kind_loss(kind, x, 0.0f, false, 0.0f, gamma, unused);
     }
   }
 
@@ -517,8 +567,17 @@ loss_rows_kernel(const LayerTab t, const LossParams p,
       // objectness target at this cell (loss_.rs:397-406); Hausdorff has no score (loss_.rs:285-288)
       const float to = haus ? p.obj_base
                             : p.obj_base + fminf(fmaxf(metric, 0.0f), 1.0f) * p.obj_coef;
-      const float lwm1 = p.has_pw ? (p.pw - 1.0f) * to : 0.0f;
-      a_obj += (double)(-to * xo) + (double)(lwm1 * softplus_f(-xo));
+      float dxo = 0.0f;  // d objectness-loss / d xo for the non-BCE kinds
+      if (p.obj_kind == YH_LOSS_BCE) {
+        const float lwm1 = p.has_pw ? (p.pw - 1.0f) * to : 0.0f;
+        a_obj += (double)(-to * xo) + (double)(lwm1 * softplus_f(-xo));
+      } else {
+        // K4 summed loss(x, 0) for this cell: replace it by loss(x, t)
+        float d0;
+        const float l0 = kind_loss(p.obj_kind, xo, 0.0f, false, 0.0f, p.gamma, d0);
+        const float lt = kind_loss(p.obj_kind, xo, to, p.has_pw != 0, p.pw, p.gamma, dxo);
+        a_obj += (double)lt - (double)l0;
+      }
       if (iou_score) iou_score[m] = metric;
       if (pred_rows) {
         float* r = pred_rows + (size_t)m * t.E;
@@ -538,7 +597,9 @@ loss_rows_kernel(const LayerTab t, const LossParams p,
         // objectness gradient with the real target (replaces K4's target-0 value)
         const float so = sigmoid_f(xo);
         float gi;
-        if (p.has_pw) {
+        if (p.obj_kind != YH_LOSS_BCE) {
+          gi = dxo;
+        } else if (p.has_pw) {
           const float tp = p.pw * to;
           gi = ((tp + 1.0f) - to) * so - tp;
         } else {
@@ -560,6 +621,28 @@ loss_rows_kernel(const LayerTab t, const LossParams p,
       const float* hp = t.head[l_r] + off_r;
       float* gp = want_grad ? row_grad + (size_t)(m0 + r) * t.E : nullptr;
       float bce = 0.f;
+      // CrossEntropyLoss (cross_entropy.rs:19-58): the dense target's arg-max (first maximum:
+      // the class, or 0 when pos == neg), log_softmax + nll per ROW
+      const int ce_t = (p.cls_pos > p.cls_neg) ? cls_r : 0;
+      float lse = 0.f;
+      if (p.cls_kind == YH_LOSS_CROSS_ENTROPY) {
+        float mx = -INFINITY;
+        for (int k = lane, j = 0; k < t.C; k += 32, ++j) {
+          const float x = j == 0 ? xc[r][0] : j == 1 ? xc[r][1] : j == 2 ? xc[r][2]
+                                                                        : hp[(size_t)(5 + k) * es_r];
+          mx = fmaxf(mx, x);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        float se = 0.f;
+        for (int k = lane, j = 0; k < t.C; k += 32, ++j) {
+          const float x = j == 0 ? xc[r][0] : j == 1 ? xc[r][1] : j == 2 ? xc[r][2]
+                                                                        : hp[(size_t)(5 + k) * es_r];
+          se += expf(x - mx);
+        }
+        se = warp_sum(se);
+        lse = mx + logf(se);
+      }
       for (int k = lane, j = 0; k < t.C; k += 32, ++j) {
         float x;
         if (j == 0) x = xc[r][0];
@@ -567,12 +650,20 @@ loss_rows_kernel(const LayerTab t, const LossParams p,
         else if (j == 2) x = xc[r][2];
         else x = hp[(size_t)(5 + k) * es_r];
         const float tt = (k == cls_r) ? p.cls_pos : p.cls_neg;
-        bce += (1.0f - tt) * x + softplus_f(-x);
-        if (want_grad) {
-          float gi = sigmoid_f(x) - tt;
+        float gi;
+        if (p.cls_kind == YH_LOSS_BCE) {
+          bce += (1.0f - tt) * x + softplus_f(-x);
+          gi = sigmoid_f(x) - tt;
           if (p.reduction == YH_REDUCTION_MEAN) gi = gi / MCf;
-          gp[5 + k] = gi * p.w_cls;
+        } else if (p.cls_kind == YH_LOSS_CROSS_ENTROPY) {
+          if (k == ce_t) bce += lse - x;
+          gi = expf(x - lse) - (k == ce_t ? 1.0f : 0.0f);
+          if (p.reduction == YH_REDUCTION_MEAN) gi = gi / Mf;  // mean over the M rows
+        } else {
+          bce += kind_loss(p.cls_kind, x, tt, false, 0.0f, p.gamma, gi);
+          if (p.reduction == YH_REDUCTION_MEAN) gi = gi / MCf;
         }
+        if (want_grad) gp[5 + k] = gi * p.w_cls;
         if (pred_rows) pred_rows[(size_t)(m0 + r) * t.E + 5 + k] = x;
       }
       bce = warp_sum(bce);
@@ -687,7 +778,9 @@ loss_finish_kernel(const LayerTab t, const GradTab g, const LossParams p,
     if (p.reduction == YH_REDUCTION_MEAN) {
       // empty inputs give 0 (loss_.rs:309-314, bce_with_logits_loss.rs:74-77)
       iou_l = M > 0 ? (float)(iou_sum / (double)M) : 0.0f;
-      cls_l = M > 0 ? (float)(cls_sum / ((double)M * (double)t.C)) : 0.0f;
+      const double cls_n = (p.cls_kind == YH_LOSS_CROSS_ENTROPY) ? (double)M
+                                                                 : (double)M * (double)t.C;
+      cls_l = M > 0 ? (float)(cls_sum / cls_n) : 0.0f;
       obj_l = (float)(obj_sum / ((double)p.B * (double)t.N));
     } else {
       iou_l = (float)iou_sum;
@@ -746,6 +839,12 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
   YH_REQUIRE(cfg->objectness_loss_weight >= 0.0, "objectness_loss_weight must be non-negative");
   YH_REQUIRE(cfg->classification_loss_weight >= 0.0,
              "classification_loss_weight must be non-negative");
+  YH_REQUIRE(cfg->focal_loss_gamma >= 0.0, "focal_loss_gamma must be non-negative");
+  YH_REQUIRE(cfg->objectness_loss_kind >= YH_LOSS_BCE && cfg->objectness_loss_kind <= YH_LOSS_L2,
+             "objectness_loss_kind=%d", cfg->objectness_loss_kind);
+  YH_REQUIRE(cfg->classification_loss_kind >= YH_LOSS_BCE &&
+                 cfg->classification_loss_kind <= YH_LOSS_CROSS_ENTROPY,
+             "classification_loss_kind=%d", cfg->classification_loss_kind);
   YH_REQUIRE(cfg->reduction == YH_REDUCTION_MEAN || cfg->reduction == YH_REDUCTION_SUM,
              "reduction %d is not supported", cfg->reduction);
   YH_REQUIRE(cfg->box_metric >= YH_METRIC_IOU && cfg->box_metric <= YH_METRIC_HAUSDORFF,
@@ -775,6 +874,9 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
   p.obj_coef = (float)cfg->smooth_objectness_coef;
   p.has_pw = cfg->has_objectness_pos_weight ? 1 : 0;
   p.pw = (float)cfg->objectness_pos_weight;
+  p.obj_kind = cfg->objectness_loss_kind;
+  p.cls_kind = cfg->classification_loss_kind;
+  p.gamma = (float)cfg->focal_loss_gamma;
 
   cudaStream_t s = (cudaStream_t)stream;
   YH_CUDA(cudaSetDevice(ws->device));
@@ -788,15 +890,18 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
   }();
   int dense_grid = ws->num_sms * dense_cps;
   if (dense_grid > kPartHalf) dense_grid = kPartHalf;
-  if (!(phases & kPhaseDense)) {
-  } else if (grad_heads) {
+  if (phases & kPhaseDense) {
+    const bool bce = p.obj_kind == YH_LOSS_BCE;
     YH_TIME(YH_K_LOSS_DENSE, s);
-    loss_dense_kernel<true><<<dense_grid, kDenseThreads, 0, s>>>(
-        tab, g, B, numel, p.w_obj, p.reduction, ws->partials);
-  } else {
-    YH_TIME(YH_K_LOSS_DENSE, s);
-    loss_dense_kernel<false><<<dense_grid, kDenseThreads, 0, s>>>(
-        tab, g, B, numel, p.w_obj, p.reduction, ws->partials);
+#define YH_DENSE(G, K)                                                   \
+  loss_dense_kernel<G, K><<<dense_grid, kDenseThreads, 0, s>>>(          \
+      tab, g, B, numel, p.w_obj, p.reduction, p.obj_kind, p.gamma, ws->partials)
+    if (grad_heads) {
+      if (bce) YH_DENSE(true, true); else YH_DENSE(true, false);
+    } else {
+      if (bce) YH_DENSE(false, true); else YH_DENSE(false, false);
+    }
+#undef YH_DENSE
   }
   if (phases & kPhaseDense) YH_LAUNCHED(s);
   int row_grid = ws->num_sms * 4;  // resident in one wave; rows beyond that grid-stride

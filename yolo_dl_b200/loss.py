@@ -142,10 +142,19 @@ class YoloLossInit:
     objectness_pos_weight: Optional[float] = None
     smooth_classification_coef: float = 0.01
     smooth_objectness_coef: float = 0.0
+    focal_loss_gamma: float = 0.0              # loss_.rs:176
+    objectness_loss_kind: str = "Bce"          # ObjectnessLossKind::{Bce,Focal,L2} (:191-196)
+    classification_loss_kind: str = "Bce"      # ClassificationLossKind::{Bce,Focal,L2,CrossEntropy} (:198-205)
     unit_upstream_grad: bool = True  # both reference call sites do total_loss.backward()
 
     def build(self) -> "YoloLoss":
         # loss_.rs:64-87
+        if not self.focal_loss_gamma >= 0.0:
+            raise ValueError("focal_loss_gamma must be non-negative")
+        if self.objectness_loss_kind.lower() not in ("bce", "focal", "l2"):
+            raise ValueError(f"unknown objectness_loss_kind {self.objectness_loss_kind}")
+        if self.classification_loss_kind.lower() not in _lib.LOSS_KINDS:
+            raise ValueError(f"unknown classification_loss_kind {self.classification_loss_kind}")
         if not 0.0 <= self.smooth_classification_coef <= 1.0:
             raise ValueError("smooth_classification_coef must be in range [0, 1]")
         if not 0.0 <= self.smooth_objectness_coef <= 1.0:
@@ -195,6 +204,9 @@ class YoloLoss:
         c.smooth_objectness_coef = init.smooth_objectness_coef
         c.has_objectness_pos_weight = 0 if init.objectness_pos_weight is None else 1
         c.objectness_pos_weight = init.objectness_pos_weight or 0.0
+        c.objectness_loss_kind = _lib.LOSS_KINDS[init.objectness_loss_kind.lower()]
+        c.classification_loss_kind = _lib.LOSS_KINDS[init.classification_loss_kind.lower()]
+        c.focal_loss_gamma = init.focal_loss_gamma
         self._cfg = c
 
     def forward_raw(self, prediction: MergedDenseDetection, target, want_grad: bool):
