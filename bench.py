@@ -42,6 +42,8 @@ def parse():
     p.add_argument("--cpu-sample", type=int, default=64, help="images per CPU-baseline pass")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--loss-exchange", default="peer", choices=["peer", "nccl"],
+                   help="N>1: in-graph peer-memory stores over NVLink (default) or a NCCL all-reduce per step")
     return p.parse_args()
 
 
@@ -50,7 +52,7 @@ def workload_config(args, world):
             "spec": "yolov4-608 (76x76,38x38,19x19; A=3; C=80; N=22743)",
             "batch_per_gpu": args.batch, "global_batch": args.batch * world,
             "gt_per_image": "U{1..30}", "box_metric": "ciou", "nms": f"conf {NMS_CONF} iou {NMS_IOU} per-class",
-            "parallelism": f"images sharded over {world} GPU(s), 5-float loss all-reduce only",
+            "parallelism": f"images sharded over {world} GPU(s); only exchange: 5 weighted loss scalars per step",
             "l2": "inputs (495 MB/GPU/step) larger than the 126 MB L2; no flush needed"}
 
 
@@ -199,11 +201,18 @@ def run_native(args):
     step = DeviceStep(spec, B, dev, nms_conf=NMS_CONF, nms_iou=NMS_IOU, by_class=BY_CLASS)
 
     # the step as a CUDA graph: 9 kernels on 4 forked/joined streams (pipeline.run_overlapped)
-    step.capture(heads, gt_d, off_d, loss_slots=2 if world > 1 else 1)
-
-    # the loss-scalar exchange data-parallel training needs: one 5-float NCCL
-    # all-reduce per step, on its own stream so that it runs under the next step's kernels
-    reducer = ydist.LossAllReduce(dev, B) if world > 1 else None
+    # the loss-scalar exchange data-parallel training needs, N > 1: the step's last
+    # kernel stores this rank's five weighted scalars into every peer's mailbox over NVLink
+    # (CUDA IPC peer memory, yolo_dl_b200/csrc/peer.cu) — part of the graph, no collective kernel
+    # and no host launch per step.  --loss-exchange nccl: one 5-float NCCL all-reduce per step on
+    # its own stream instead (the baseline this replaces).
+    peer = reducer = None
+    if world > 1 and args.loss_exchange == "peer":
+        peer = ydist.PeerLossExchange(dev, B)
+        step.capture(heads, gt_d, off_d, publisher=peer)
+    else:
+        step.capture(heads, gt_d, off_d, loss_slots=2 if world > 1 else 1)
+        reducer = ydist.LossAllReduce(dev, B) if world > 1 else None
 
     def one_step():
         step.replay()
@@ -229,6 +238,24 @@ def run_native(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t)
     value = world * B * K / (ms * 1e-3)
+
+    # the combined loss of the last step: what the peer mailboxes hold vs a NCCL all-reduce of the
+    # same weighted scalars (outside the timed region; a check, not part of the step)
+    exchange = None
+    if world > 1:
+        chk = ydist.weighted_mean_losses(step.losses4, B)
+        torch.cuda.synchronize()
+        if peer is not None:
+            dist.barrier()
+            comb, seq = peer.collect()
+            exchange = {"kind": "peer-memory stores over NVLink, in the step graph (csrc/peer.cu)",
+                        "combined_total": float(comb[0]), "nccl_allreduce_check": float(chk[0]),
+                        "published_steps": seq}
+            assert seq == W + K, (seq, W + K)
+            assert abs(float(comb[0]) - float(chk[0])) <= 1e-6 * abs(float(chk[0])) + 1e-7, (comb, chk)
+        else:
+            exchange = {"kind": "NCCL all-reduce per step on its own stream",
+                        "combined_total": float(chk[0])}
 
     # the same 9 kernels launched one after another on one stream (no graph), for comparison
     Ks = max(3, min(K, 50))
@@ -371,7 +398,7 @@ def run_native(args):
                 "dtype": "f32", "data": "synthetic", "config": workload_config(args, world),
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches,
                 "execution": "CUDA graph of 9 kernels on 4 forked/joined streams, replayed once per step",
-                "sequential_ms_per_step": seq_ms,
+                "sequential_ms_per_step": seq_ms, "loss_exchange": exchange,
                 "clocks": clk.summary(), "matches_per_step": M, "detections_per_step": Kdet,
                 "loss": float(step.losses4[0])}
         print(json.dumps(line), flush=True)

@@ -269,6 +269,28 @@ int yh_average_precision(const int32_t* det_gt_dev, const double* det_iou_dev,
                          int max_detections_per_problem, const double* iou_thresholds_dev,
                          int num_thresholds, int n_points, double* out_ap_dev, void* stream);
 
+/* ---- §8e: the data-parallel loss exchange as peer-memory stores over NVLink / NVSwitch.
+ * Replaces the per-step master-device averaging of the loss scalars
+ * (`train/src/train/multi_gpu.rs:188-195`, `yolo-dl/src/loss/loss_.rs:527-577`): sum_g loss_g*B_g /
+ * sum_g B_g.  Every rank (one process per GPU of ONE node) creates a mailbox
+ * [slots][world][8 f32], exchanges the 64-byte CUDA IPC handle with its peers (any transport:
+ * torch.distributed all_gather here) and opens theirs.  yh_loss_publish — one 32-thread kernel,
+ * capturable in a CUDA graph, enqueued after the loss of a step — writes this rank's
+ * [B_g*total, B_g*iou, B_g*cls, B_g*obj, B_g, -, -, seq] into entry [seq % slots][rank] of every
+ * peer's mailbox (peer_mails[r], r = 0..world-1, own mailbox at [rank]); the sequence number lives
+ * on the device and advances with every launch.  yh_loss_collect (synchronises `stream`) returns
+ * the combined [total, iou, cls, obj] of the newest step all ranks have published, and its
+ * sequence number (0 = none complete yet).  No collective kernel, no host work per step. */
+typedef struct YhMailbox YhMailbox;
+int yh_peer_mailbox_create(int device, int world, int slots, YhMailbox** out, void** mail_dev,
+                           unsigned char* handle64);
+int yh_peer_mailbox_open(int device, const unsigned char* handle64, void** peer_mail);
+int yh_peer_mailbox_close(int device, void* peer_mail);
+int yh_peer_mailbox_destroy(YhMailbox* m);
+int yh_loss_publish(YhMailbox* m, const float* losses4_dev, float weight, void* const* peer_mails,
+                    int rank, void* stream);
+int yh_loss_collect(YhMailbox* m, float* out4, unsigned* out_seq, void* stream);
+
 /* ---- a14: YoloInference::forward post-pass (`yolo-dl/src/loss/inference.rs:50-77`):
  * among kept rows of the same (batch, instance) keep the one with max confidence.
  * max_by_key keeps the LAST maximum: equal confidences keep the later row.

@@ -83,6 +83,13 @@ SYMBOLS = {
                                 c_void_p]),
     "yh_average_precision": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
                                      c_void_p, c_int, c_int, c_void_p, c_void_p]),
+    "yh_peer_mailbox_create": (c_int, [c_int, c_int, c_int, POINTER(c_void_p), POINTER(c_void_p),
+                                       c_void_p]),
+    "yh_peer_mailbox_open": (c_int, [c_int, c_void_p, POINTER(c_void_p)]),
+    "yh_peer_mailbox_close": (c_int, [c_int, c_void_p]),
+    "yh_peer_mailbox_destroy": (c_int, [c_void_p]),
+    "yh_loss_publish": (c_int, [c_void_p, c_void_p, c_float, POINTER(c_void_p), c_int, c_void_p]),
+    "yh_loss_collect": (c_int, [c_void_p, POINTER(c_float), POINTER(ctypes.c_uint32), c_void_p]),
     "yh_read_counts": (c_int, [c_void_p, c_void_p, POINTER(c_int32), c_void_p, POINTER(c_int32),
                                c_void_p]),
     "yh_launch_count": (c_int64, [c_int]),
@@ -94,7 +101,7 @@ SYMBOLS = {
 KERNEL_NAMES = ["decode_kernel", "assign_slots_kernel", "assign_emit_kernel", "loss_dense_kernel",
                 "loss_rows_kernel", "nms_filter_kernel", "nms_segment_kernel", "nms_emit_kernel",
                 "nms_pack_kernel", "pick_kernel", "benchmark_kernel",
-                "match_det_gt_kernel", "ap_kernel", "loss_finish_kernel"]
+                "match_det_gt_kernel", "ap_kernel", "loss_finish_kernel", "loss_publish_kernel"]
 
 _lib = None
 

@@ -43,7 +43,7 @@ int64_t& launch_counter();
 enum KernelId {
   YH_K_DECODE = 0, YH_K_ASSIGN_SLOTS, YH_K_ASSIGN_EMIT, YH_K_LOSS_DENSE, YH_K_LOSS_ROWS,
   YH_K_NMS_FILTER, YH_K_NMS_SEGMENT, YH_K_NMS_EMIT, YH_K_NMS_PACK, YH_K_PICK, YH_K_BENCHMARK,
-  YH_K_MATCH_DET_GT, YH_K_AP, YH_K_LOSS_FINISH, YH_K_COUNT
+  YH_K_MATCH_DET_GT, YH_K_AP, YH_K_LOSS_FINISH, YH_K_LOSS_PUBLISH, YH_K_COUNT
 };
 void timing_begin(int id, cudaStream_t s);  // no-ops unless timing is enabled on this thread
 void timing_end(cudaStream_t s);

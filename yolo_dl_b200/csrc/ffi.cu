@@ -278,6 +278,7 @@ int yh_workspace_create(int device, int max_batch, int64_t max_instances, int ca
   // the matcher's slot table is EMPTY between calls (assign.cu)
   if (cudaMemset(ws->slot_dist, 0xff, slots * sizeof(unsigned long long)) != cudaSuccess ||
       cudaMemset(ws->slot_gt, 0x7f, slots * sizeof(int)) != cudaSuccess ||
+      cudaMemset(ws->cand_count, 0, (size_t)max_batch * sizeof(int)) != cudaSuccess ||
       cudaMemset(ws->ticket, 0, 64) != cudaSuccess ||
       cudaMemset(ws->err_flag, 0, 64) != cudaSuccess ||
       cudaMallocHost((void**)&ws->host_counts, ((size_t)max_batch + 8) * sizeof(int32_t)) !=

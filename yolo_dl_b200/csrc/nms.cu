@@ -321,6 +321,9 @@ nms_segment_kernel(const P prov, const SegView v, const double iou_thr) {
 
   sort_keys(keys, K, s_keys);
   __syncthreads();
+  // every thread has read the count: leave it 0 for the next filter pass (the per-call memset
+  // node this replaces sat behind the dense store stream in the overlapped step)
+  if (threadIdx.x == 0) v.count[seg] = 0;
 
   // the sort tile becomes the kept-box cache; the bit matrix lives behind it
   float4* c_box = reinterpret_cast<float4*>(s_keys);
@@ -612,7 +615,6 @@ int yh_nms(YhWorkspace* ws, const float* const* heads, const YhLayer* layers, in
              (long long)prov.t.N * C);
   cudaStream_t s = (cudaStream_t)stream;
   YH_CUDA(cudaSetDevice(ws->device));
-  YH_CUDA(cudaMemsetAsync(ws->cand_count, 0, (size_t)B * sizeof(int), s));
   SegView v = make_view(ws);
   const int per_cta = kFilterThreads * kFilterPer;
   dim3 grid((prov.t.N + per_cta - 1) / per_cta, B);

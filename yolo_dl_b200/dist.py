@@ -115,3 +115,67 @@ class LossAllReduce:
         self.done2[k].record(self.stream)
         self.buf = weighted5
         self.done = self.done2[k]
+
+
+class PeerLossExchange:
+    """The same exchange WITHOUT a collective: every rank's step writes its five weighted scalars
+    straight into all peers' mailboxes over NVLink / NVSwitch (CUDA IPC peer memory) from a
+    32-thread kernel that is part of the step's CUDA graph — no NCCL kernel, no host launch per
+    step (include/yolohot.h §8e, csrc/peer.cu).  `publish(losses4, stream)` enqueues (capturable);
+    `collect()` returns (combined [total, iou, cls, obj], sequence number) of the newest step all
+    ranks have published.  One node only (CUDA IPC); torch.distributed is used once, to exchange
+    the 64-byte handles."""
+
+    def __init__(self, device: torch.device, local_batch: int, slots: int = 8, group=None):
+        import ctypes
+        from . import _lib
+        self._lib_mod, self.lib = _lib, _lib.load()
+        self.dev, self.weight = device, float(local_batch)
+        active = dist.is_available() and dist.is_initialized()
+        self.world = dist.get_world_size(group) if active else 1
+        self.rank = dist.get_rank(group) if active else 0
+        self.handle = ctypes.c_void_p()
+        mail = ctypes.c_void_p()
+        h = (ctypes.c_ubyte * 64)()
+        _lib.check(self.lib.yh_peer_mailbox_create(device.index or 0, self.world, slots,
+                                                   ctypes.byref(self.handle), ctypes.byref(mail), h))
+        mine = torch.tensor(list(h), dtype=torch.uint8, device=device)
+        if self.world > 1:
+            allh = [torch.empty_like(mine) for _ in range(self.world)]
+            dist.all_gather(allh, mine, group=group)
+        else:
+            allh = [mine]
+        self.peers = (ctypes.c_void_p * self.world)()
+        self._opened = []
+        for r in range(self.world):
+            if r == self.rank:
+                self.peers[r] = mail.value
+                continue
+            hb = (ctypes.c_ubyte * 64)(*allh[r].cpu().tolist())
+            p = ctypes.c_void_p()
+            _lib.check(self.lib.yh_peer_mailbox_open(device.index or 0, hb, ctypes.byref(p)))
+            self.peers[r] = p.value
+            self._opened.append(p.value)
+        if self.world > 1:
+            dist.barrier(group=group)  # every mailbox is mapped before anyone publishes
+
+    def publish(self, losses4: torch.Tensor, stream=None):
+        s = stream if stream is not None else torch.cuda.current_stream(self.dev).cuda_stream
+        self._lib_mod.check(self.lib.yh_loss_publish(self.handle, losses4.data_ptr(), self.weight,
+                                                     self.peers, self.rank, s))
+
+    def collect(self):
+        import ctypes
+        out = (ctypes.c_float * 4)()
+        seq = ctypes.c_uint32(0)
+        self._lib_mod.check(self.lib.yh_loss_collect(self.handle, out, ctypes.byref(seq),
+                                                     torch.cuda.current_stream(self.dev).cuda_stream))
+        return torch.tensor(list(out), dtype=torch.float32), int(seq.value)
+
+    def close(self):
+        for p in self._opened:
+            self.lib.yh_peer_mailbox_close(self.dev.index or 0, p)
+        self._opened = []
+        if self.handle:
+            self.lib.yh_peer_mailbox_destroy(self.handle)
+            self.handle = None

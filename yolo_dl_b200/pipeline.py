@@ -7,6 +7,7 @@ host synchronisation.  `HostStep` is the same step for callers whose tensors liv
 the step, D2H of losses / matches / detections and of the head gradients.
 """
 import ctypes
+import os
 from typing import List, Optional, Sequence
 
 import torch
@@ -137,8 +138,12 @@ class DeviceStep:
         fork.record(main)
         for st in self._side:
             st.wait_event(fork)
-        _lib.check(self.lib.yh_loss_dense(self.ws.handle, hp, self.layers, self.L, self.B, self.C, self.cfg,
-                                          self._grad_ptrs, main.cuda_stream))
+        # enqueue the store stream last: the short latency-bound kernels of the other branches then
+        # get their CTAs placed before loss_dense's 2368 CTAs fill every SM (tools/timeline.py)
+        dense_last = os.environ.get("YH_DENSE_LAST", "1") == "1"
+        if not dense_last:
+            _lib.check(self.lib.yh_loss_dense(self.ws.handle, hp, self.layers, self.L, self.B, self.C,
+                                              self.cfg, self._grad_ptrs, main.cuda_stream))
         self._assign(gt_dev, off_dev, s_asg.cuda_stream)
         _lib.check(self.lib.yh_loss_rows_compute(
             self.ws.handle, hp, self.layers, self.L, self.B, self.C, self.m_batch.data_ptr(),
@@ -147,6 +152,9 @@ class DeviceStep:
             self.pred_rows.data_ptr(), 1 if self._grad_ptrs is not None else 0, s_asg.cuda_stream))
         self._nms(hp, s_nms.cuda_stream)
         self._decode(hp, s_dec.cuda_stream)
+        if dense_last:
+            _lib.check(self.lib.yh_loss_dense(self.ws.handle, hp, self.layers, self.L, self.B, self.C,
+                                              self.cfg, self._grad_ptrs, main.cuda_stream))
         joins = []
         for st in self._side:
             e = torch.cuda.Event()
@@ -160,13 +168,16 @@ class DeviceStep:
         main.wait_event(joins[0])
         main.wait_event(joins[2])
 
-    def capture(self, heads, gt_dev, off_dev, loss_slots: int = 1):
+    def capture(self, heads, gt_dev, off_dev, loss_slots: int = 1, publisher=None):
         """Captures `run_overlapped` on these buffers into a CUDA graph; `replay()` launches it.
         The captured pointers are those of `heads`/`gt_dev`/`off_dev`: refill them in place.
         `loss_slots` > 1 captures that many copies of the graph that differ only in the
         `losses4` buffer they write and replays them round-robin, so that a consumer on another
         stream (the data-parallel loss all-reduce, dist.LossAllReduce) can still read step i's
-        scalars while step i+1 runs."""
+        scalars while step i+1 runs.
+        `publisher` (dist.PeerLossExchange): its 32-thread kernel becomes the last node of the
+        graph and writes this rank's weighted loss scalars into every peer's mailbox over NVLink —
+        the data-parallel loss exchange with no collective and no host work per step."""
         self._keep = (list(heads), gt_dev, off_dev)
         self.run_overlapped(heads, gt_dev, off_dev)  # warm: module attributes, streams
         torch.cuda.synchronize(self.dev)
@@ -185,7 +196,9 @@ class DeviceStep:
             before = int(self.lib.yh_launch_count(0))
             with torch.cuda.graph(g, stream=cap):
                 self.run_overlapped(heads, gt_dev, off_dev)
-                if loss_slots > 1:
+                if publisher is not None:
+                    publisher.publish(self.losses4, cap.cuda_stream)
+                elif loss_slots > 1:
                     torch.mul(self._l5_ring[k], float(self.B), out=self._w5_ring[k])
             self.kernels_in_graph = int(self.lib.yh_launch_count(0)) - before
             self._graphs.append(g)
