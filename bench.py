@@ -42,6 +42,7 @@ def parse():
     p.add_argument("--cpu-sample", type=int, default=64, help="images per CPU-baseline pass")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--no-extras", action="store_true", help="skip the side numbers of BASELINE configs 2-4")
     p.add_argument("--loss-exchange", default="peer", choices=["peer", "nccl"],
                    help="N>1: in-graph peer-memory stores over NVLink (default) or a NCCL all-reduce per step")
     return p.parse_args()
@@ -162,6 +163,83 @@ def run_reference(args):
             "note": "oracle restatement of the reference's tch CPU path (same ATen kernels via PyTorch, "
                     "C matcher, torchvision batched_nms for tch-nms); the Rust reference cannot be built here"}
     print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------------
+# side numbers (BASELINE.json configs[2..4]; parity cases in tests/, reported here, not the metric)
+# ----------------------------------------------------------------------------------
+def side_configs(dev):
+    import torch
+    import yolo_dl_b200 as yh
+    from yolo_dl_b200 import synth
+    from yolo_dl_b200.pipeline import DeviceStep
+
+    def graph_us(fn, reps=200):
+        fn()
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        cap = torch.cuda.Stream(dev)
+        with torch.cuda.graph(g, stream=cap):
+            fn(cap.cuda_stream)
+        for _ in range(5):
+            g.replay()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            g.replay()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / reps * 1e3
+
+    out = {}
+    # configs[2]: YOLOv4-tiny 416 decode + NMS, batch 256 (latency-bound small-head path)
+    spec = synth.yolov4_tiny_416()
+    B = 256
+    heads = synth.make_heads(spec, B, SEED + 2, device=dev)
+    st = DeviceStep(spec, B, dev, nms_conf=NMS_CONF, nms_iou=NMS_IOU, by_class=BY_CLASS, with_grad=False)
+    hp = yh._lib.ptr_array(heads)
+
+    def tiny(s=None):
+        s = s if s is not None else torch.cuda.current_stream(dev).cuda_stream
+        st._decode(hp, s)
+        st._nms(hp, s)
+    us = graph_us(tiny)
+    out["yolov4_tiny_416_decode_nms_b256"] = {"us_per_batch": us, "launches_per_batch": 4,
+                                              "images_per_s": B / (us * 1e-6)}
+    del st, heads
+    # configs[3]: YOLOv4-CSP 640, 300 GT boxes per image (30 % clustered), target assignment only
+    spec = synth.yolov4_csp_640()
+    B = 64
+    targets = synth.make_targets(spec, B, SEED + 3, n_min=300, n_max=300, clustered=0.3)
+    gt_h, off_h = yh.pack_labels(targets)
+    gt_d, off_d = gt_h.to(dev), off_h.to(dev)
+    st = DeviceStep(spec, B, dev, with_grad=False, max_gt=300 * B)
+
+    def assign(s=None):
+        st._assign(gt_d, off_d, s if s is not None else torch.cuda.current_stream(dev).cuda_stream)
+    us = graph_us(assign)
+    M, _ = st.counts()
+    out["yolov4_csp_640_assign_300gt_b64"] = {"us_per_batch": us, "matches": M, "gt_boxes": 300 * B,
+                                              "gt_boxes_per_s": 300 * B / (us * 1e-6)}
+    del st
+    # configs[4]: grouped NMS on explicit candidates (the tch_nms::nms_by_scores drop-in), 80 classes
+    sweep = {}
+    for Kc in (1000, 4000, 16000, 65536):
+        ltrb, scores, grp = synth.make_nms_boxes(Kc, SEED + Kc, num_groups=80)
+        args_d = [torch.from_numpy(x).to(dev) for x in (ltrb, scores, grp)]
+        yh.nms_by_scores(*args_d, 0.5)
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps = 10
+        a.record()
+        for _ in range(reps):
+            kept = yh.nms_by_scores(*args_d, 0.5)
+        b.record()
+        torch.cuda.synchronize()
+        ms = a.elapsed_time(b) / reps
+        sweep[str(Kc)] = {"ms": ms, "kept": int(kept.numel()), "candidates_per_s": Kc / (ms * 1e-3)}
+    out["nms_by_scores_one_segment_80_classes"] = sweep
+    return out
 
 
 # ----------------------------------------------------------------------------------
@@ -385,6 +463,10 @@ def run_native(args):
                "loss": float(hl[0]), "matches": hM, "detections": hK}
         del pipe, host_heads
 
+    extras = None
+    if rank == 0 and world == 1 and not args.no_extras:
+        extras = side_configs(dev)
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         v, per, cores = time_cpu_reference(args.cpu_sample, 20, 1)
@@ -398,7 +480,7 @@ def run_native(args):
                 "dtype": "f32", "data": "synthetic", "config": workload_config(args, world),
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches,
                 "execution": "CUDA graph of 9 kernels on 4 forked/joined streams, replayed once per step",
-                "sequential_ms_per_step": seq_ms, "loss_exchange": exchange,
+                "sequential_ms_per_step": seq_ms, "loss_exchange": exchange, "other_configs": extras,
                 "clocks": clk.summary(), "matches_per_step": M, "detections_per_step": Kdet,
                 "loss": float(step.losses4[0])}
         print(json.dumps(line), flush=True)

@@ -176,6 +176,8 @@ struct YhWorkspace {
   long long* kept_grp;            // [max_batch * cand_stride] suppression group of a kept box
   int* kept_count;                // [max_batch]
 
+  int* by_ints;                   // yh_nms_by_scores buckets: count | off | cursor | kept | total
+
   int* err_flag;                  // device: sticky overflow flag
   int32_t* host_counts;           // pinned, [max_batch + 8]
 };

@@ -207,6 +207,7 @@ int yh_workspace_destroy(YhWorkspace* ws) {
   cudaFree(ws->kept_box);
   cudaFree(ws->kept_count);
   cudaFree(ws->kept_grp);
+  cudaFree(ws->by_ints);
   cudaFree(ws->err_flag);
   if (ws->host_counts) cudaFreeHost(ws->host_counts);
   delete ws;
@@ -273,12 +274,14 @@ int yh_workspace_create(int device, int max_batch, int64_t max_instances, int ca
   YH_ALLOC(ws->kept_box, cands * sizeof(float4));
   YH_ALLOC(ws->kept_count, (size_t)max_batch * sizeof(int));
   YH_ALLOC(ws->kept_grp, cands * sizeof(long long));
+  YH_ALLOC(ws->by_ints, 2048 * sizeof(int));
   YH_ALLOC(ws->err_flag, 64);
 #undef YH_ALLOC
   // the matcher's slot table is EMPTY between calls (assign.cu)
   if (cudaMemset(ws->slot_dist, 0xff, slots * sizeof(unsigned long long)) != cudaSuccess ||
       cudaMemset(ws->slot_gt, 0x7f, slots * sizeof(int)) != cudaSuccess ||
       cudaMemset(ws->cand_count, 0, (size_t)max_batch * sizeof(int)) != cudaSuccess ||
+      cudaMemset(ws->by_ints, 0, 2048 * sizeof(int)) != cudaSuccess ||
       cudaMemset(ws->ticket, 0, 64) != cudaSuccess ||
       cudaMemset(ws->err_flag, 0, 64) != cudaSuccess ||
       cudaMallocHost((void**)&ws->host_counts, ((size_t)max_batch + 8) * sizeof(int32_t)) !=

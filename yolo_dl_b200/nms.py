@@ -133,7 +133,8 @@ def nms_by_scores(ltrb: torch.Tensor, scores: torch.Tensor, groups: torch.Tensor
         raise ValueError("size mismatch")
     dev = ltrb.device
     ws = _ws_by_scores.setdefault(dev.index, Workspace())
-    h = ws.ensure(dev, 1, 1, max(K, 2))
+    # room for one power-of-two padded segment per group bucket (csrc/nms.cu, kBySegs)
+    h = ws.ensure(dev, 1, 1, max(2 * K + 512, 2))
     keep = torch.empty(max(K, 1), dtype=torch.int64, device=dev)
     n = torch.zeros(1, dtype=torch.int32, device=dev)
     lib = _lib.load()
