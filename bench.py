@@ -324,12 +324,14 @@ def run_native(args):
         chk = ydist.weighted_mean_losses(step.losses4, B)
         torch.cuda.synchronize()
         if peer is not None:
+            peer.publish(step.losses4)   # the graph publishes one step behind: flush the last one
+            torch.cuda.synchronize()
             dist.barrier()
             comb, seq = peer.collect()
             exchange = {"kind": "peer-memory stores over NVLink, in the step graph (csrc/peer.cu)",
                         "combined_total": float(comb[0]), "nccl_allreduce_check": float(chk[0]),
                         "published_steps": seq}
-            assert seq == W + K, (seq, W + K)
+            assert seq == W + K + 1, (seq, W + K + 1)
             assert abs(float(comb[0]) - float(chk[0])) <= 1e-6 * abs(float(chk[0])) + 1e-7, (comb, chk)
         else:
             exchange = {"kind": "NCCL all-reduce per step on its own stream",

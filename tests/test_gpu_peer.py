@@ -83,3 +83,35 @@ def test_mailbox_two_ranks_equals_nccl_allreduce():
         want = [(3 * 5 * k + 5 * 10 * k) / 8 for k in (1, 2, 3, 4)]
         assert comb == pytest.approx(want, rel=1e-6)
         assert comb == pytest.approx(ref, rel=1e-6)
+
+
+def test_step_graph_publishes_one_step_behind(dev):
+    """DeviceStep.capture(publisher=...): replay i stores the scalars of replay i-1 (under its own
+    kernels); one explicit publish after the last replay flushes."""
+    import yolo_dl_b200 as yh
+    from yolo_dl_b200 import dist as ydist, synth
+    from yolo_dl_b200.pipeline import DeviceStep
+    spec, B = synth.small_spec(), 3
+    heads = [h.to(dev) for h in synth.make_heads(spec, B, 5)]
+    gt, off = yh.pack_labels(synth.make_targets(spec, B, 5, n_max=6))
+    gt, off = gt.to(dev), off.to(dev)
+    step = DeviceStep(spec, B, dev)
+    ex = ydist.PeerLossExchange(dev, local_batch=B, slots=4)
+    step.capture(heads, gt, off, publisher=ex)
+    assert step.kernels_in_graph == DeviceStep.KERNELS_PER_STEP + 1
+    for _ in range(3):
+        step.replay()
+    torch.cuda.synchronize()
+    first = step.losses4.clone()
+    comb, seq = ex.collect()
+    assert seq == 3 and torch.allclose(comb, first.cpu())       # same inputs: same scalars every step
+    heads[0].mul_(0.5)                                           # new inputs -> new loss
+    step.replay()
+    torch.cuda.synchronize()
+    comb, seq = ex.collect()
+    assert seq == 4 and torch.allclose(comb, first.cpu())       # still the previous step's
+    ex.publish(step.losses4)
+    torch.cuda.synchronize()
+    comb, seq = ex.collect()
+    assert seq == 5 and torch.allclose(comb, step.losses4.cpu()) and not torch.allclose(comb, first.cpu())
+    ex.close()

@@ -64,6 +64,7 @@ class DeviceStep:
         # staging of the matched-row gradients: reserved now, graphs cannot allocate
         _lib.check(self.lib.yh_workspace_reserve_rows(self.ws.handle, self.mcap, self.C))
         self._side = None
+        self._pub_stream = None
         self._graph = None
         self.kernels_in_graph = 0
 
@@ -109,7 +110,7 @@ class DeviceStep:
                                    self.K.data_ptr(), self.kcap, s))
 
     # -- the same 9 kernels as a fork/join over four streams --------------------------------
-    def run_overlapped(self, heads, gt_dev, off_dev):
+    def run_overlapped(self, heads, gt_dev, off_dev, publisher=None, lagged_publish=True):
         """The step as the dependency graph it really is (the reference runs it as one sequence,
         train/src/train/single_gpu.rs:152-186):
 
@@ -138,6 +139,18 @@ class DeviceStep:
         fork.record(main)
         for st in self._side:
             st.wait_event(fork)
+        pub_done = None
+        if publisher is not None and lagged_publish:
+            # the data-parallel loss exchange (dist.PeerLossExchange) one step behind: the stores
+            # of step i-1's scalars into the peers' mailboxes (two system-scope fences over
+            # NVLink) run on their own branch under step i's kernels instead of at its tail;
+            # loss_finish, which overwrites losses4, waits for them
+            if self._pub_stream is None:
+                self._pub_stream = torch.cuda.Stream(self.dev)
+            self._pub_stream.wait_event(fork)
+            publisher.publish(self.losses4, self._pub_stream.cuda_stream)
+            pub_done = torch.cuda.Event()
+            pub_done.record(self._pub_stream)
         # enqueue the store stream last: the short latency-bound kernels of the other branches then
         # get their CTAs placed before loss_dense's 2368 CTAs fill every SM (tools/timeline.py)
         dense_last = os.environ.get("YH_DENSE_LAST", "1") == "1"
@@ -161,10 +174,14 @@ class DeviceStep:
             e.record(st)
             joins.append(e)
         main.wait_event(joins[1])
+        if pub_done is not None:
+            main.wait_event(pub_done)
         _lib.check(self.lib.yh_loss_finish(
             self.ws.handle, self.layers, self.L, self.B, self.C, self.m_batch.data_ptr(),
             self.m_flat.data_ptr(), self.M.data_ptr(), self.mcap, self.cfg, self.losses4.data_ptr(),
             self._grad_ptrs, main.cuda_stream))
+        if publisher is not None and not lagged_publish:
+            publisher.publish(self.losses4, main.cuda_stream)
         main.wait_event(joins[0])
         main.wait_event(joins[2])
 
@@ -175,9 +192,11 @@ class DeviceStep:
         `losses4` buffer they write and replays them round-robin, so that a consumer on another
         stream (the data-parallel loss all-reduce, dist.LossAllReduce) can still read step i's
         scalars while step i+1 runs.
-        `publisher` (dist.PeerLossExchange): its 32-thread kernel becomes the last node of the
-        graph and writes this rank's weighted loss scalars into every peer's mailbox over NVLink —
-        the data-parallel loss exchange with no collective and no host work per step."""
+        `publisher` (dist.PeerLossExchange): its 32-thread kernel becomes a node of the graph
+        and writes this rank's weighted loss scalars into every peer's mailbox over NVLink — the
+        data-parallel loss exchange with no collective and no host work per step.  It runs ONE
+        STEP BEHIND (replay i publishes the scalars of replay i-1, under replay i's kernels):
+        call `publisher.publish(step.losses4)` once after the last replay to flush."""
         self._keep = (list(heads), gt_dev, off_dev)
         self.run_overlapped(heads, gt_dev, off_dev)  # warm: module attributes, streams
         torch.cuda.synchronize(self.dev)
@@ -195,10 +214,8 @@ class DeviceStep:
             g = torch.cuda.CUDAGraph()
             before = int(self.lib.yh_launch_count(0))
             with torch.cuda.graph(g, stream=cap):
-                self.run_overlapped(heads, gt_dev, off_dev)
-                if publisher is not None:
-                    publisher.publish(self.losses4, cap.cuda_stream)
-                elif loss_slots > 1:
+                self.run_overlapped(heads, gt_dev, off_dev, publisher=publisher)
+                if publisher is None and loss_slots > 1:
                     torch.mul(self._l5_ring[k], float(self.B), out=self._w5_ring[k])
             self.kernels_in_graph = int(self.lib.yh_launch_count(0)) - before
             self._graphs.append(g)
