@@ -22,4 +22,14 @@ arithmetic lives in the un-vendored git dependency `tch-nms` @
     NMS vs torchvision.ops.batched_nms; closed-form BCE/IoU gradients vs autograd);
   * golden vectors generated from this oracle in this container (tests/golden/, script
     tests/golden/make_golden.py) so that any later drift is caught.
+PINNED by code or known answers of the reference tree itself:
+  * evaluation metrics (oracle/evaluation.py): the expected values of the reference's own tests
+    pred_gt_matching.rs:149-240 and average_precision.rs:560-705 (tests/test_oracle_eval.py);
+  * the DenseDetectionTensor container operations: the reference's `cat_test`,
+    dense_detection_tensor.rs:582-728 (tests/test_tensors_known_answers.py);
+  * the box-metric family (oracle/box.py), SECONDARY: outputs of the vendored darknet C code
+    (darknet-test/darknet/src/box.c:135-256) compiled in place into oracle/_ref by
+    oracle/build.py, committed as tests/golden/darknet_box.npz (tests/test_oracle_ref.py).
+    IoU / GIoU / DIoU agree to 2e-6; CIoU's alpha*v term agrees in magnitude with the opposite
+    sign (yolo-dl's cycxhw.rs:119 adds it).
 """
