@@ -66,6 +66,50 @@ __global__ void __launch_bounds__(128) fill_tma(char* __restrict__ p, long long 
   }
 }
 
+
+// E: one tile per CTA, no loop (the hardware's in-order CTA dispatch keeps the set of tiles
+// being written at any moment small and contiguous)
+template <int UNROLL>
+__global__ void __launch_bounds__(256) fill_once(float4* __restrict__ p, long long nquads) {
+  const long long tile = 256LL * UNROLL;
+  const long long t = blockIdx.x;
+  const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+  float4* q = p + t * tile + threadIdx.x;
+#pragma unroll
+  for (int u = 0; u < UNROLL; ++u)
+    if (t * tile + threadIdx.x + u * 256 < nquads) __stcs(q + u * 256, z);
+}
+
+// F: persistent, but every CTA owns a CONTIGUOUS range of tiles
+template <int UNROLL>
+__global__ void __launch_bounds__(256) fill_chunk(float4* __restrict__ p, long long nquads) {
+  const long long tile = 256LL * UNROLL;
+  const long long ntiles = (nquads + tile - 1) / tile;
+  const long long per = (ntiles + gridDim.x - 1) / gridDim.x;
+  const long long t0 = blockIdx.x * per, t1 = min(t0 + per, ntiles);
+  const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (long long t = t0; t < t1; ++t) {
+    float4* q = p + t * tile + threadIdx.x;
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u)
+      if (t * tile + threadIdx.x + u * 256 < nquads) __stcs(q + u * 256, z);
+  }
+}
+
+// G: grid-stride tiles, but a WARP writes 4 KB contiguous (8 x 512 B back to back)
+__global__ void __launch_bounds__(256) fill_warpc(float4* __restrict__ p, long long nquads) {
+  const long long tile = 256LL * 8;
+  const long long ntiles = (nquads + tile - 1) / tile;
+  const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  for (long long t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    float4* q = p + t * tile + wid * 256 + lane;
+#pragma unroll
+    for (int u = 0; u < 8; ++u)
+      if (t * tile + wid * 256 + lane + u * 32 < nquads) __stcs(q + u * 32, z);
+  }
+}
+
 template <typename F>
 static float timeit(const char* name, double bytes, F f) {
   cudaEvent_t a, b;
@@ -104,6 +148,20 @@ int main() {
     char nm[64];
     snprintf(nm, 64, "st4.cs unroll8 grid %dxSM", k);
     timeit(nm, nbytes, [&] { fill_st4<8, 0><<<sms * k, 256>>>((float4*)p, nq); });
+  }
+  {
+    const long long t8 = (nq + 2047) / 2048, t4 = (nq + 1023) / 1024, t2 = (nq + 511) / 512, t1 = (nq + 255) / 256;
+    timeit("once 32KB/CTA grid=ntiles", nbytes, [&] { fill_once<8><<<(unsigned)t8, 256>>>((float4*)p, nq); });
+    timeit("once 16KB/CTA grid=ntiles", nbytes, [&] { fill_once<4><<<(unsigned)t4, 256>>>((float4*)p, nq); });
+    timeit("once 8KB/CTA grid=ntiles", nbytes, [&] { fill_once<2><<<(unsigned)t2, 256>>>((float4*)p, nq); });
+    timeit("once 4KB/CTA grid=ntiles", nbytes, [&] { fill_once<1><<<(unsigned)t1, 256>>>((float4*)p, nq); });
+    for (int k : {4, 8, 16}) {
+      char nm[64];
+      snprintf(nm, 64, "chunk-contiguous unroll8 grid %dxSM", k);
+      timeit(nm, nbytes, [&] { fill_chunk<8><<<sms * k, 256>>>((float4*)p, nq); });
+      snprintf(nm, 64, "warp-contiguous 4KB grid %dxSM", k);
+      timeit(nm, nbytes, [&] { fill_warpc<<<sms * k, 256>>>((float4*)p, nq); });
+    }
   }
   timeit("st4.cs unroll4 grid 8xSM", nbytes, [&] { fill_st4<4, 0><<<sms * 8, 256>>>((float4*)p, nq); });
   timeit("st4.cs unroll16 grid 8xSM", nbytes, [&] { fill_st4<16, 0><<<sms * 8, 256>>>((float4*)p, nq); });

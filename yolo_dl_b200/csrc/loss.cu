@@ -107,6 +107,14 @@ __device__ __forceinline__ float kind_loss(const int kind, const float x, const 
 //     that hold an objectness element are NOT written here but by pass 1, which spreads all
 //     B*N/4 of them evenly over the grid (left in the tiles they serialise a few CTAs on
 //     load latency + transcendental math while the others have long finished: 97 -> ~85 us).
+// per-layer prefixes of loss_dense_kernel's two passes, computed on the host
+struct DenseTab {
+  int L;
+  long long run[YH_MAX_LAYERS];              // A*HW: floats per entry per image
+  long long tile_prefix[YH_MAX_LAYERS + 1];  // pass 2, in tiles
+  long long qprefix[YH_MAX_LAYERS + 1];      // pass 1, in quads
+};
+
 constexpr int kTileUnroll = 8;
 constexpr int kTileQuads = kDenseThreads * kTileUnroll;  // 2048 quads = 8192 floats = 32 KB
 constexpr int kTileFloats = kTileQuads * 4;
@@ -116,112 +124,49 @@ template <bool GRAD, bool BCE>
 __global__ void __launch_bounds__(kDenseThreads)
 loss_dense_kernel(const LayerTab t, const GradTab g, const int B, const float numel,
                   const float w_obj, const int reduction, const int kind, const float gamma,
-                  double* __restrict__ partials) {
+                  double* __restrict__ partials, const int n_obj, const DenseTab d) {
   double acc = 0.0;
   if (GRAD) {
-    // ---- pass 1: the quads that hold at least one objectness element ---------------------
-    // (B*N/4 of them, spread evenly over the whole grid so that their load latency and
-    // transcendental math are paid in parallel, before the store stream starts).  Slot j of
-    // image b of layer l is quad floor((b*per_img + 4*run)/4) + j, if it still starts before
-    // the plane's end.
-    {
-      long long qprefix[YH_MAX_LAYERS + 1];
-      qprefix[0] = 0;
-#pragma unroll
-      for (int l = 0; l < YH_MAX_LAYERS; ++l)
-        qprefix[l + 1] = qprefix[l] + ((l < t.L) ? (long long)B * ((t.A[l] * t.HW[l]) / 4 + 2) : 0LL);
-      const long long total = qprefix[YH_MAX_LAYERS];
-      const long long stride = (long long)gridDim.x * kDenseThreads;
-      for (long long i = (long long)blockIdx.x * kDenseThreads + threadIdx.x; i < total; i += stride) {
-        int l = 0;
-#pragma unroll
-        for (int k = 1; k < YH_MAX_LAYERS; ++k)
-          if (k < t.L && i >= qprefix[k]) l = k;
-        const int run = t.A[l] * t.HW[l];
-        const int slots = run / 4 + 2;
-        const long long li = i - qprefix[l];
-        const long long b = li / slots;
-        const int j = (int)(li - b * slots);
-        const long long per_img = (long long)run * t.E;
-        const long long len = (long long)B * per_img;
-        const long long o0 = b * per_img + 4LL * run, o1 = o0 + run;  // obj plane of image b
-        const long long idx = (o0 / 4 + j) * 4;                        // first float of the quad
-        if (idx >= o1) continue;
-        const float* __restrict__ hp = t.head[l] + idx;
-        float* __restrict__ gp = g.grad[l] + idx;
-        const bool full = idx + 3 < len;
-        float x[4] = {0.f, 0.f, 0.f, 0.f};
-        if (idx >= o0 && idx + 3 < o1) {
-          const float4 v = __ldcs(reinterpret_cast<const float4*>(hp));
-          x[0] = v.x; x[1] = v.y; x[2] = v.z; x[3] = v.w;
-        } else {
-#pragma unroll
-          for (int k = 0; k < 4; ++k)
-            if (idx + k >= o0 && idx + k < o1) x[k] = __ldcs(hp + k);
-        }
-        float v[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          if (idx + k >= o0 && idx + k < o1) {
-            float gi;
-            if (BCE) {
-              acc += (double)softplus_f(x[k]);
-              // BCE backward, target 0: sigmoid(x) [/numel for Mean] * upstream w_obj
-              gi = sigmoid_f(x[k]);
-            } else {
-              acc += (double)kind_loss(kind, x[k], 0.0f, false, 0.0f, gamma, gi);
-            }
-            if (reduction == YH_REDUCTION_MEAN) gi = gi / numel;
-            v[k] = gi * w_obj;
-          }
-        }
-        if (full) {
-          st_stream4(reinterpret_cast<float4*>(gp), make_float4(v[0], v[1], v[2], v[3]));
-        } else {
-#pragma unroll
-          for (int k = 0; k < 4; ++k)
-            if (idx + k < len) st_stream1(gp + k, v[k]);
-        }
-      }
-    }
-
-    // ---- pass 2: zeros everywhere else -------------------------------------------------------
-    long long prefix[YH_MAX_LAYERS + 1];  // in tiles
-    prefix[0] = 0;
-#pragma unroll
-    for (int l = 0; l < YH_MAX_LAYERS; ++l) {
-      long long n = 0;
-      if (l < t.L) {
-        const long long quads = ((long long)B * t.A[l] * t.E * t.HW[l] + 3) / 4;
-        n = (quads + kTileQuads - 1) / kTileQuads;
-      }
-      prefix[l + 1] = prefix[l] + n;
-    }
-    const long long total = prefix[YH_MAX_LAYERS];
-    const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (long long tile = blockIdx.x; tile < total; tile += gridDim.x) {
-      int l = 0;
+    // NOT a persistent kernel: the first n_obj CTAs do pass 1, every later CTA writes exactly one
+    // tile of pass 2 and exits.  The hardware hands CTAs out in index order, so the tiles being
+    // written at any moment are a small contiguous window of the tensor: 6.9-7.0 TB/s on B200
+    // where a grid-stride loop over the same tiles reaches 6.0-6.3 and cudaMemset 6.65
+    // (tools/fill_bench.cu, profiles/r1f_fill_bench.txt).  The objectness CTAs go first so that
+    // their load latency and transcendental math are hidden under the store stream.
+    // A one-tile CTA cannot afford a prologue: the per-layer prefixes come precomputed in `d`
+    // and the layer's fields are picked with compile-time indices (a run-time index into a
+    // kernel-parameter array makes every thread copy that array to local memory first).
+    const int E = t.E;
+    if ((int)blockIdx.x >= n_obj) {
+      // ---- pass 2: one 32 KB tile of zeros -------------------------------------------------
+      const long long tile = (long long)blockIdx.x - n_obj;
+      long long run = d.run[0], tp = 0;
+      float* __restrict__ gl = g.grad[0];
 #pragma unroll
       for (int k = 1; k < YH_MAX_LAYERS; ++k)
-        if (k < t.L && tile >= prefix[k]) l = k;
-      const long long run = (long long)t.A[l] * t.HW[l];  // floats per entry per image
-      const long long per_img = run * t.E;                // floats per image
+        if (k < d.L && tile >= d.tile_prefix[k]) {
+          run = d.run[k];
+          tp = d.tile_prefix[k];
+          gl = g.grad[k];
+        }
+      const long long per_img = run * E;                 // floats per image
       const long long len = (long long)B * per_img;
-      const long long idx0 = (tile - prefix[l]) * kTileFloats;  // first float of the tile
+      const long long idx0 = (tile - tp) * kTileFloats;  // first float of the tile
       // its offset inside the image (32-bit modulo whenever the layer tensor allows it)
       const long long r0 = (len < (1LL << 31)) ? (long long)((unsigned)idx0 % (unsigned)per_img)
                                                : idx0 % per_img;
-      const long long o0 = 4 * run, o1 = 5 * run;               // obj plane of an image
-      float* __restrict__ gbase = g.grad[l] + idx0;
+      const long long o0 = 4 * run, o1 = 5 * run;        // obj plane of an image
+      float* __restrict__ gbase = gl + idx0;
       const bool whole = idx0 + kTileFloats <= len;
       const bool one_wrap = per_img >= kTileFloats + 4;
       const bool touches = !one_wrap || (r0 + kTileFloats > o0 && r0 < o1) ||
                            (r0 + kTileFloats > per_img + o0);
+      const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
       if (whole && !touches) {
         float4* q = reinterpret_cast<float4*>(gbase) + threadIdx.x;
 #pragma unroll
         for (int u = 0; u < kTileUnroll; ++u) st_stream4(q + u * kDenseThreads, zero4);
-        continue;
+        return;
       }
       // a tile that meets an objectness plane or the end of the tensor: per-quad test, quads
       // with an objectness element belong to pass 1
@@ -246,6 +191,70 @@ loss_dense_kernel(const LayerTab t, const GradTab g, const int B, const float nu
           for (int k = 0; k < 4; ++k)
             if (idx + k < len) st_stream1(gp + k, 0.0f);
         }
+      }
+      return;
+    }
+    // ---- pass 1: the quads that hold at least one objectness element ---------------------
+    // (B*N/4 of them, spread evenly over the n_obj leading CTAs).  Slot j of image b of layer l
+    // is quad floor((b*per_img + 4*run)/4) + j, if it still starts before the plane's end.
+    const long long total = d.qprefix[YH_MAX_LAYERS];
+    const long long stride = (long long)n_obj * kDenseThreads;
+    for (long long i = (long long)blockIdx.x * kDenseThreads + threadIdx.x; i < total; i += stride) {
+      int run = (int)d.run[0];
+      long long qp = 0;
+      const float* __restrict__ hl = t.head[0];
+      float* __restrict__ gl = g.grad[0];
+#pragma unroll
+      for (int k = 1; k < YH_MAX_LAYERS; ++k)
+        if (k < d.L && i >= d.qprefix[k]) {
+          run = (int)d.run[k];
+          qp = d.qprefix[k];
+          hl = t.head[k];
+          gl = g.grad[k];
+        }
+      const int slots = run / 4 + 2;
+      const long long li = i - qp;
+      const long long b = li / slots;
+      const int j = (int)(li - b * slots);
+      const long long per_img = (long long)run * E;
+      const long long len = (long long)B * per_img;
+      const long long o0 = b * per_img + 4LL * run, o1 = o0 + run;  // obj plane of image b
+      const long long idx = (o0 / 4 + j) * 4;                        // first float of the quad
+      if (idx >= o1) continue;
+      const float* __restrict__ hp = hl + idx;
+      float* __restrict__ gp = gl + idx;
+      const bool full = idx + 3 < len;
+      float x[4] = {0.f, 0.f, 0.f, 0.f};
+      if (idx >= o0 && idx + 3 < o1) {
+        const float4 v = __ldcs(reinterpret_cast<const float4*>(hp));
+        x[0] = v.x; x[1] = v.y; x[2] = v.z; x[3] = v.w;
+      } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          if (idx + k >= o0 && idx + k < o1) x[k] = __ldcs(hp + k);
+      }
+      float v[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        if (idx + k >= o0 && idx + k < o1) {
+          float gi;
+          if (BCE) {
+            acc += (double)softplus_f(x[k]);
+            // BCE backward, target 0: sigmoid(x) [/numel for Mean] * upstream w_obj
+            gi = sigmoid_f(x[k]);
+          } else {
+            acc += (double)kind_loss(kind, x[k], 0.0f, false, 0.0f, gamma, gi);
+          }
+          if (reduction == YH_REDUCTION_MEAN) gi = gi / numel;
+          v[k] = gi * w_obj;
+        }
+      }
+      if (full) {
+        st_stream4(reinterpret_cast<float4*>(gp), make_float4(v[0], v[1], v[2], v[3]));
+      } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          if (idx + k < len) st_stream1(gp + k, v[k]);
       }
     }
   } else {
@@ -881,21 +890,37 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
   cudaStream_t s = (cudaStream_t)stream;
   YH_CUDA(cudaSetDevice(ws->device));
   const float numel = (float)((long long)B * tab.N);
-  // 16 CTAs per SM (two waves of 8 resident): measured best on B200 both alone (88 us vs 94 us
-  // at 2..8 CTAs/SM) and inside the overlapped step (profiles/README.md, sweep r1c)
+  // objectness CTAs (and the whole grid of the forward-only form) per SM
   static const int dense_cps = []() {  // tuning knob for sweeps (profiles/README.md)
     const char* e = getenv("YH_DENSE_CTAS_PER_SM");
     const int v = e ? atoi(e) : 0;
-    return v > 0 ? v : 16;
+    return v > 0 ? v : 4;
   }();
   int dense_grid = ws->num_sms * dense_cps;
   if (dense_grid > kPartHalf) dense_grid = kPartHalf;
+  // with a gradient: dense_grid objectness CTAs followed by one CTA per 32 KB tile
+  DenseTab dt;
+  memset(&dt, 0, sizeof(dt));
+  dt.L = L;
+  for (int l = 0; l < YH_MAX_LAYERS; ++l) {
+    long long tiles = 0, oq = 0;
+    if (l < L) {
+      dt.run[l] = (long long)tab.A[l] * tab.HW[l];
+      const long long quads = ((long long)B * dt.run[l] * tab.E + 3) / 4;
+      tiles = (quads + kTileQuads - 1) / kTileQuads;
+      oq = (long long)B * (dt.run[l] / 4 + 2);
+    }
+    dt.tile_prefix[l + 1] = dt.tile_prefix[l] + tiles;
+    dt.qprefix[l + 1] = dt.qprefix[l] + oq;
+  }
+  const long long dense_tiles = dt.tile_prefix[YH_MAX_LAYERS];
+  YH_REQUIRE(dense_tiles + dense_grid < (1LL << 31), "head tensors too large for one launch");
   if (phases & kPhaseDense) {
     const bool bce = p.obj_kind == YH_LOSS_BCE;
     YH_TIME(YH_K_LOSS_DENSE, s);
-#define YH_DENSE(G, K)                                                   \
-  loss_dense_kernel<G, K><<<dense_grid, kDenseThreads, 0, s>>>(          \
-      tab, g, B, numel, p.w_obj, p.reduction, p.obj_kind, p.gamma, ws->partials)
+#define YH_DENSE(G, K)                                                                       \
+  loss_dense_kernel<G, K><<<(unsigned)(dense_grid + (G ? dense_tiles : 0)), kDenseThreads, 0, s>>>( \
+      tab, g, B, numel, p.w_obj, p.reduction, p.obj_kind, p.gamma, ws->partials, dense_grid, dt)
     if (grad_heads) {
       if (bce) YH_DENSE(true, true); else YH_DENSE(true, false);
     } else {
