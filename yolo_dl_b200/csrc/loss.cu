@@ -890,11 +890,13 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
   cudaStream_t s = (cudaStream_t)stream;
   YH_CUDA(cudaSetDevice(ws->device));
   const float numel = (float)((long long)B * tab.N);
-  // objectness CTAs (and the whole grid of the forward-only form) per SM
-  static const int dense_cps = []() {  // tuning knob for sweeps (profiles/README.md)
+  // objectness CTAs (and the whole grid of the forward-only form) per SM.  Sweep on B200
+  // (profiles/README.md, r1f): 1 -> 78.4 us, 2 -> 77.1, 3 -> 77.9, 4 -> 79.1, 8 -> 80.6; tiles of
+  // 16 KB 105 us (the CTA prologue shows), 32 KB 77.7, 64 KB 77.1.
+  static const int dense_cps = []() {  // tuning knob for sweeps
     const char* e = getenv("YH_DENSE_CTAS_PER_SM");
     const int v = e ? atoi(e) : 0;
-    return v > 0 ? v : 4;
+    return v > 0 ? v : 2;
   }();
   int dense_grid = ws->num_sms * dense_cps;
   if (dense_grid > kPartHalf) dense_grid = kPartHalf;
