@@ -27,6 +27,8 @@
 // i.e. the drop-in for tch_nms::nms_by_scores itself.
 #include <math.h>
 
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace yh {
@@ -116,9 +118,9 @@ __device__ __forceinline__ bool suppresses(const float4 a, const float area_a, c
 // all ceil(C/32) class loads in flight together.  (The first version — one instance per thread,
 // class loads one at a time — ran as five waves of warps each waiting on four dependent DRAM
 // round trips: 33 us for 5.8 MB of compulsory reads.)
-constexpr int kFilterPer = 4;
 constexpr int kFilterClsRegs = 3;  // class loads in flight per expansion (C <= 96), tail loops
 
+template <int kFilterPer>
 __global__ void __launch_bounds__(kFilterThreads)
 nms_filter_kernel(const LayerTab t, const float thr, unsigned long long* __restrict__ keys,
                   const int stride, const int cap, int* __restrict__ count,
@@ -719,11 +721,26 @@ int yh_nms(YhWorkspace* ws, const float* const* heads, const YhLayer* layers, in
   cudaStream_t s = (cudaStream_t)stream;
   YH_CUDA(cudaSetDevice(ws->device));
   SegView v = make_view(ws);
-  const int per_cta = kFilterThreads * kFilterPer;
+  // instances per thread.  Sweep inside the overlapped step on B200 (r1f): 8 -> 193.1 us per step,
+  // 4 -> 191.3, 2 -> 191.0, 1 -> 184.4..189.9 (kernel alone 46 / 38 / 36 / 35.5 us): many short
+  // CTAs interleave better with the other kernels of the step than few long ones.
+  static const int filter_per = []() {
+    const char* e = getenv("YH_FILTER_PER");
+    const int v = e ? atoi(e) : 0;
+    return (v == 1 || v == 2 || v == 4 || v == 8) ? v : 1;
+  }();
+  const int per_cta = kFilterThreads * filter_per;
   dim3 grid((prov.t.N + per_cta - 1) / per_cta, B);
   YH_TIME(YH_K_NMS_FILTER, s);
-  nms_filter_kernel<<<grid, kFilterThreads, 0, s>>>(prov.t, (float)confidence_threshold, v.keys,
-                                                    (int)v.stride, v.cap, v.count, ws->err_flag);
+#define YH_FILTER(P)                                                                          \
+  nms_filter_kernel<P><<<grid, kFilterThreads, 0, s>>>(prov.t, (float)confidence_threshold,   \
+                                                       v.keys, (int)v.stride, v.cap, v.count, \
+                                                       ws->err_flag)
+  if (filter_per == 2) YH_FILTER(2);
+  else if (filter_per == 4) YH_FILTER(4);
+  else if (filter_per == 8) YH_FILTER(8);
+  else YH_FILTER(1);
+#undef YH_FILTER
   YH_LAUNCHED(s);
   rc = launch_segments(prov, v, B, iou_threshold, s);
   if (rc) return rc;
