@@ -2,17 +2,16 @@
 // optionally fused with the layer merge of MergedDenseDetection::from_detection_tensors
 // (tch-goodies/src/detection/merged_dense_detection.rs:60-91).
 //
-// HBM-bound streaming kernel: per instance it reads the 4 box logits (entries 0..3 of the
-// entry-major head, each a unit-stride run along the cell index) and writes cy,cx,h,w.
-// Algorithmic traffic 32 B per instance.  The four outputs are independent
-// functions of one logit each (cy of entry 0, cx of 1, h of 2, w of 3), so the grid is
-// (chunks, B, 4 entries) where a chunk is kDecodeThreads*4 consecutive cells of ONE
-// (layer, anchor) plane: a CTA never straddles planes, so there is no per-thread search for
-// the layer, the entry is block-uniform (one instantiation per entry), and the grid term
-// arange(size)/size of detect_2d.rs:122-133 is a <= 1024-entry table built once per CTA in
-// shared memory (the reference caches the same table per (H,W), detect_2d.rs:162-238).
-// A thread: one 16-byte load, four sigmoids, one 16-byte store.  19x19 / 13x13 planes and odd
-// batch strides are not 16-byte aligned: those use scalar accesses, still coalesced.
+// Streaming kernel: per instance it reads the 4 box logits (entries 0..3 of the entry-major
+// head, each a unit-stride run along the cell index) and writes cy,cx,h,w.  Algorithmic traffic
+// 32 B per instance.  The grid is (chunks, B) where a chunk is kDecodeThreads*4
+// consecutive cells of ONE (layer, anchor): a CTA never straddles planes, so there is no
+// per-thread search for the layer, and the grid terms arange(size)/size of detect_2d.rs:122-133
+// are two <= 1024-entry tables built once per CTA in shared memory (the reference caches the
+// same tables per (H,W), detect_2d.rs:162-238).  A thread: four 16-byte loads (one per box
+// entry, all in flight before the tables are built), sixteen sigmoids, four 16-byte stores.
+// 19x19 / 13x13 planes and odd batch strides are not 16-byte aligned: those use scalar accesses,
+// still coalesced.
 #include "common.cuh"
 
 namespace yh {
@@ -26,10 +25,15 @@ struct ChunkTab {
   int cstart[YH_MAX_LAYERS];  // first chunk of the layer
 };
 
-template <int E>
-__device__ __forceinline__ void decode_plane(const LayerTab& t, const ChunkTab& ct,
-                                             float* __restrict__ outp, long long out_stride,
-                                             float* s_tab) {
+// One CTA = 1024 cells of one (image, layer, anchor) for ALL FOUR box entries: every thread has
+// four 16-byte loads in flight (cy, cx, h, w logits of its 4 cells) while the CTA fills the two
+// grid-offset tables, instead of one load per thread and four times as many CTAs (r1e: 6912 CTAs
+// of one load each, 25 us for 46 MB — bound by per-CTA latency, not by bandwidth or math).
+__global__ void __launch_bounds__(kDecodeThreads)
+decode_kernel(const LayerTab t, const ChunkTab ct, float* __restrict__ cy, float* __restrict__ cx,
+              float* __restrict__ h, float* __restrict__ w, long long out_stride) {
+  __shared__ float s_row[kGridTabMax];
+  __shared__ float s_col[kGridTabMax];
   const int b = blockIdx.y;
   int l = 0;
 #pragma unroll
@@ -38,65 +42,63 @@ __device__ __forceinline__ void decode_plane(const LayerTab& t, const ChunkTab& 
   const int rel = blockIdx.x - ct.cstart[l];
   const int anchor = rel / ct.cpp[l];
   const int chunk = rel - anchor * ct.cpp[l];
-  const int H = t.H[l], W = t.W[l], HW = t.HW[l];
-  const float size = (E == 0) ? (float)H : (float)W;
-  const int tab_n = (E == 0) ? H : W;
-  const bool use_tab = E < 2 && tab_n <= kGridTabMax;
-  if (use_tab) {
-    for (int i = threadIdx.x; i < tab_n; i += kDecodeThreads) s_tab[i] = (float)i / size;
-    __syncthreads();
-  }
-  const int cell0 = chunk * kDecodeChunk + threadIdx.x * 4;
-  if (cell0 >= HW) return;
-  const float anc = (E == 2) ? t.ah[l][anchor] : t.aw[l][anchor];
-  const float* __restrict__ p =
-      t.head[l] + ((size_t)b * (size_t)(t.A[l] * t.E) + (size_t)(E * t.A[l] + anchor)) * (size_t)HW + cell0;
-  float* __restrict__ out =
-      outp + (size_t)b * (size_t)out_stride + (size_t)t.start[l] + (size_t)anchor * HW + cell0;
-  int row = cell0 / W, col = cell0 - row * W;
-  const int cnt = min(4, HW - cell0);
+  const int H = t.H[l], W = t.W[l], HW = t.HW[l], A = t.A[l];
+  const float Hf = (float)H, Wf = (float)W;
+  const bool tab_h = H <= kGridTabMax, tab_w = W <= kGridTabMax;
 
-  float a[4] = {0.f, 0.f, 0.f, 0.f};
-  if (cnt == 4 && ((uintptr_t)p & 15) == 0) {
-    const float4 v = __ldcs(reinterpret_cast<const float4*>(p));
-    a[0] = v.x; a[1] = v.y; a[2] = v.z; a[3] = v.w;
-  } else {
+  const int cell0 = chunk * kDecodeChunk + threadIdx.x * 4;
+  const bool live = cell0 < HW;
+  const int cnt = live ? min(4, HW - cell0) : 0;
+  // entry e of (b, anchor) starts e*A*HW floats after entry 0 (channel = e*A + anchor)
+  const size_t es = (size_t)A * (size_t)HW;
+  const float* __restrict__ p0 =
+      t.head[l] + ((size_t)b * (size_t)(A * t.E) + (size_t)anchor) * (size_t)HW + cell0;
+  float a[4][4];
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
-      if (i < cnt) a[i] = __ldcs(p + i);
-  }
-  float o[4];
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const float s = sigmoid_f(a[i]);
-    if (E < 2) {
-      const int idx = (E == 0) ? row : col;
-      // (sigmoid*2 - 0.5)/size + arange(size)[idx]/size   == decode_center()
-      const float g = use_tab ? s_tab[idx] : (float)idx / size;
-      o[i] = (s * 2.0f - 0.5f) / size + g;
-      if (++col == W) { col = 0; ++row; }
+  for (int e = 0; e < 4; ++e) {
+    const float* p = p0 + (size_t)e * es;
+    if (cnt == 4 && ((uintptr_t)p & 15) == 0) {
+      const float4 v = __ldcs(reinterpret_cast<const float4*>(p));
+      a[e][0] = v.x; a[e][1] = v.y; a[e][2] = v.z; a[e][3] = v.w;
     } else {
-      o[i] = decode_size(s, anc);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) a[e][i] = (i < cnt) ? __ldcs(p + i) : 0.0f;
     }
   }
-  if (cnt == 4 && ((uintptr_t)out & 15) == 0) {
-    st_stream4(reinterpret_cast<float4*>(out), make_float4(o[0], o[1], o[2], o[3]));
-  } else {
-#pragma unroll
-    for (int i = 0; i < 4; ++i)
-      if (i < cnt) st_stream1(out + i, o[i]);
-  }
-}
+  // arange(size)[idx]/size, one IEEE division per table entry instead of one per element
+  if (tab_h)
+    for (int i = threadIdx.x; i < H; i += kDecodeThreads) s_row[i] = (float)i / Hf;
+  if (tab_w)
+    for (int i = threadIdx.x; i < W; i += kDecodeThreads) s_col[i] = (float)i / Wf;
+  __syncthreads();
+  if (!live) return;
 
-__global__ void __launch_bounds__(kDecodeThreads)
-decode_kernel(const LayerTab t, const ChunkTab ct, float* __restrict__ cy, float* __restrict__ cx,
-              float* __restrict__ h, float* __restrict__ w, long long out_stride) {
-  __shared__ float s_tab[kGridTabMax];
-  switch (blockIdx.z) {  // block-uniform
-    case 0: decode_plane<0>(t, ct, cy, out_stride, s_tab); break;
-    case 1: decode_plane<1>(t, ct, cx, out_stride, s_tab); break;
-    case 2: decode_plane<2>(t, ct, h, out_stride, s_tab); break;
-    default: decode_plane<3>(t, ct, w, out_stride, s_tab); break;
+  const float ah = t.ah[l][anchor], aw = t.aw[l][anchor];
+  int row = cell0 / W, col = cell0 - row * W;
+  float o[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    // (sigmoid*2 - 0.5)/size + arange(size)[idx]/size   == decode_center()
+    const float gr = tab_h ? s_row[row] : (float)row / Hf;
+    const float gc = tab_w ? s_col[col] : (float)col / Wf;
+    o[0][i] = (sigmoid_f(a[0][i]) * 2.0f - 0.5f) / Hf + gr;
+    o[1][i] = (sigmoid_f(a[1][i]) * 2.0f - 0.5f) / Wf + gc;
+    o[2][i] = decode_size(sigmoid_f(a[2][i]), ah);
+    o[3][i] = decode_size(sigmoid_f(a[3][i]), aw);
+    if (++col == W) { col = 0; ++row; if (row >= H) row = H - 1; }
+  }
+  const size_t off = (size_t)b * (size_t)out_stride + (size_t)t.start[l] + (size_t)anchor * HW + cell0;
+  float* outs[4] = {cy + off, cx + off, h + off, w + off};
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    float* out = outs[e];
+    if (cnt == 4 && ((uintptr_t)out & 15) == 0) {
+      st_stream4(reinterpret_cast<float4*>(out), make_float4(o[e][0], o[e][1], o[e][2], o[e][3]));
+    } else {
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        if (i < cnt) st_stream1(out + i, o[e][i]);
+    }
   }
 }
 
@@ -113,7 +115,7 @@ static int launch_decode(const LayerTab& tab, int B, float* cy, float* cx, float
     ct.cstart[l] = chunks;
     if (l < tab.L) chunks += ct.cpp[l] * tab.A[l];
   }
-  dim3 grid(chunks, B, 4);
+  dim3 grid(chunks, B);
   YH_TIME(YH_K_DECODE, s);
   decode_kernel<<<grid, kDecodeThreads, 0, s>>>(tab, ct, cy, cx, h, w, (long long)out_stride);
   YH_LAUNCHED(s);
