@@ -157,6 +157,10 @@ int yh_assign(YhWorkspace* ws, const double* gt_dev, const int32_t* gt_offsets_d
  *   iou_score_dev [cap] box metric per matched row (nullable)          (:296-299)
  *   pred_rows_dev [cap, 5+C] gathered cy,cx,h,w,obj_logit,class_logit — the
  *                 `MatchingOutput.pred` rows (`merged_dense_detection.rs:280-307`), nullable
+ * The match list must be in the order yh_assign emits it — ascending (batch, flat), no
+ * duplicates (what `MatchingOutput::cat_mini_batches` of per-image lists also gives): the
+ * gradient scatter merges neighbouring matched cells into one store.  Anything else is reported
+ * by the next yh_read_counts as YH_ERR_INVALID.
  *   grad_heads    L device pointers, each `[B, A*(5+C), H, W]`: d total_loss / d head,
  *                 i.e. what `total_loss.backward()` delivers to the backbone
  *                 (`train/src/train/single_gpu.rs:161-168`). NULL = forward only. */

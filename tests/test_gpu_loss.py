@@ -211,3 +211,32 @@ def test_full_size_properties_batch64(dev):
     for a, h in zip(g1, heads):
         assert torch.equal(a * 2, h.grad)
     assert torch.allclose(out2.total_loss, out.total_loss * 2, rtol=1e-6)
+
+
+def test_unsorted_match_list_is_reported(dev):
+    """The gradient scatter merges neighbouring matched cells and therefore needs the match list
+    in yh_assign's order (ascending (batch, flat)); any other order must fail loudly at the next
+    yh_read_counts, not scatter wrong values quietly."""
+    from yolo_dl_b200 import _lib
+    from yolo_dl_b200.pipeline import DeviceStep
+    spec = synth.small_spec()
+    B = 3
+    heads = [h.to(dev) for h in synth.make_heads(spec, B, 5)]
+    gt_h, off_h = yh.pack_labels(synth.make_targets(spec, B, 5, n_max=6))
+    step = DeviceStep(spec, B, dev)
+    s = torch.cuda.current_stream(dev).cuda_stream
+    step._assign(gt_h.to(dev), off_h.to(dev), s)
+    hp = _lib.ptr_array(heads)
+    step._loss(step.lib.yh_loss_fwd_bwd, hp, s)
+    M, _ = step.counts()  # sorted list: fine
+    assert M > 2
+    for t in (step.m_batch, step.m_flat, step.m_class):
+        t[:M] = t[:M].flip(0)
+    step.m_target[:M] = step.m_target[:M].flip(0)
+    step._loss(step.lib.yh_loss_fwd_bwd, hp, s)
+    with pytest.raises(yh.YoloHotError) as e:
+        step.counts()
+    assert "not sorted" in str(e.value)
+    step._assign(gt_h.to(dev), off_h.to(dev), s)
+    step._loss(step.lib.yh_loss_fwd_bwd, hp, s)
+    assert step.counts()[0] == M  # the flag is cleared by the read

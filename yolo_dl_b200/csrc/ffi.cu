@@ -308,6 +308,11 @@ int yh_read_counts(YhWorkspace* ws, const int32_t* M_dev, int32_t* M_host, const
   YH_CUDA(cudaStreamSynchronize(s));
   if (M_host) *M_host = h[0];
   if (K_host) *K_host = h[1];
+  if (h[2] & 8) {
+    yh::set_error("the match list given to the loss is not sorted by (batch, flat) with unique "
+                  "entries (yh_assign emits it that way; flag=%d)", h[2]);
+    return YH_ERR_INVALID;
+  }
   if (h[2] != 0) {
     yh::set_error("a device buffer overflowed (flag=%d): 1=matches, 2=nms candidates, "
                   "4=nms outputs",

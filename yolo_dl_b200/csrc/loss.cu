@@ -720,20 +720,77 @@ loss_finish_kernel(const LayerTab t, const GradTab g, const LossParams p,
                    const int* __restrict__ M_dev, const int capacity,
                    const float* __restrict__ row_grad, const double* __restrict__ partials,
                    const int n_dense_partials, const int n_row_partials,
-                   float* __restrict__ losses4) {
+                   float* __restrict__ losses4, int* __restrict__ err_flag) {
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int warps = kFinishThreads / 32;
   const int M = min(*M_dev, capacity);
   if (g.grad[0] != nullptr && row_grad != nullptr) {
+    // The scatter is bound by the NUMBER of store requests (one per matched element, each to its
+    // own sector), not by bytes.  Matched cells come in clusters (a label takes a cell and its
+    // left/right/top/bottom neighbours) and the match list is sorted by (image, flat), so rows
+    // m-3..m+3 are the only ones that can share an aligned 4-float quad with row m: the row with
+    // the lowest flat of a quad stores the whole quad (its members' values, zeros elsewhere —
+    // what loss_dense wrote there) with ONE 16-byte store and the other members store nothing.
+    // Not for the objectness entry (its neighbours hold sigmoid values, not zeros) and not for a
+    // quad that crosses the end of its entry run: those elements are stored one by one.
     for (int m = blockIdx.x * warps + wid; m < M; m += gridDim.x * warps) {
-      const int b = (int)__ldg(m_batch + m);
-      const int flat = (int)__ldg(m_flat + m);
+      const int kk = lane - 3;  // lanes 0..6 look at rows m-3 .. m+3
+      long long nb = -1;
+      int nflat = 0;
+      if (lane < 7 && m + kk >= 0 && m + kk < M) {
+        nb = __ldg(m_batch + m + kk);
+        nflat = (int)__ldg(m_flat + m + kk);
+      }
+      const int b = (int)__shfl_sync(0xffffffffu, nb, 3);
+      const int flat = __shfl_sync(0xffffffffu, nflat, 3);
       const Cell c = locate(t, flat);
       const int l = c.layer;
-      const size_t es = (size_t)t.A[l] * (size_t)t.HW[l];
+      const int esi = t.A[l] * t.HW[l];
+      const size_t es = (size_t)esi;
+      const int j = flat - t.start[l];  // position inside the entry run
+      const int dk = nflat - flat;
+      const bool near = lane < 7 && nb == (long long)b && dk >= -3 && dk <= 3 &&
+                        nflat >= t.start[l] && nflat < t.start[l] + esi;
+      const unsigned near_mask = __ballot_sync(0xffffffffu, near);  // bit 3 = this row
+      // the merge below relies on the order yh_assign emits: report anything else loudly
+      // (yh_read_counts -> YH_ERR_INVALID) instead of scattering wrong values quietly
+      if (lane == 2 && nb >= 0 && (nb > (long long)b || (nb == (long long)b && nflat >= flat)))
+        atomicOr(err_flag, 8);
+      int d[7];  // flat distance of rows m-3 .. m+3 (meaningful where near_mask has the bit)
+#pragma unroll
+      for (int k = 0; k < 7; ++k) d[k] = __shfl_sync(0xffffffffu, dk, k);
       float* gp = g.grad[l] + head_offset(t, l, b, c.anchor, c.cell);
       const float* src = row_grad + (size_t)m * t.E;
-      for (int e = lane; e < t.E; e += 32) gp[(size_t)e * es] = __ldcs(src + e);
+      for (int e = lane; e < t.E; e += 32) {
+        const float v = __ldcs(src + e);
+        const long long q = ((long long)b * t.E + e) * (long long)es + j;  // float index in the tensor
+        const int a = (int)(q & 3);
+        if (e == 4 || j - a < 0 || j - a + 3 >= esi) {
+          gp[(size_t)e * es] = v;
+          continue;
+        }
+        // members of this element's quad among the neighbouring rows: 0 <= a + d <= 3
+        float o[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          if (i == a) o[i] = v;
+        bool lead = true;
+#pragma unroll
+        for (int k = 0; k < 7; ++k) {
+          if (k == 3) continue;
+          const int pos = a + d[k];
+          const bool in = ((near_mask >> k) & 1u) && pos >= 0 && pos <= 3;
+          if (in && k < 3) lead = false;  // a row with a lower flat stores the quad
+          if (in && k > 3) {
+            const float vk = __ldcs(row_grad + (size_t)(m + k - 3) * t.E + e);
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              if (i == pos) o[i] = vk;
+          }
+        }
+        if (lead)
+          *reinterpret_cast<float4*>(g.grad[l] + (q - a)) = make_float4(o[0], o[1], o[2], o[3]);
+      }
     }
   }
   if (blockIdx.x != 0) return;
@@ -959,7 +1016,8 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
     YH_TIME(YH_K_LOSS_FINISH, s);
     loss_finish_kernel<<<fin_grid, kFinishThreads, 0, s>>>(
         tab, g, p, (const long long*)m_batch, (const long long*)m_flat, M_dev, capacity,
-        grad_heads ? ws->row_grad : nullptr, ws->partials, dense_grid, row_grid, losses4_dev);
+        grad_heads ? ws->row_grad : nullptr, ws->partials, dense_grid, row_grid, losses4_dev,
+        ws->err_flag);
     YH_LAUNCHED(s);
   }
   return YH_OK;
