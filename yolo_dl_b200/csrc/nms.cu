@@ -773,7 +773,15 @@ int yh_nms_by_scores(YhWorkspace* ws, const float* ltrb, const float* scores,
   ArrayBoxes prov;
   prov.ltrb = ltrb;
   prov.groups = (const long long*)groups;
-  if (K > 2048 && 2LL * K + 2LL * kBySegs <= room) {
+  // rows above which the bucketed path is used.  B200, 80 groups (tools/nms_small_sweep.py):
+  // 1000 rows 0.42 ms as one segment vs 0.10 ms bucketed, 2000 rows 0.92 vs 0.115; with a single
+  // group the buckets cost 0.02 ms extra; below ~256 rows both are at the launch floor.
+  static const int by_min = []() {
+    const char* e = getenv("YH_BY_MIN");
+    const int v = e ? atoi(e) : 0;
+    return v > 0 ? v : 256;
+  }();
+  if (K > by_min && 2LL * K + 2LL * kBySegs <= room) {
     // many rows: one segment per group bucket, all buckets in parallel
     int* by_count = ws->by_ints;
     int* by_off = by_count + kBySegs;
