@@ -620,43 +620,72 @@ by_fill_kernel(const float* __restrict__ scores, const long long* __restrict__ g
   keys[(size_t)off[b] + pos] = make_key(scores[i], (unsigned)i);
 }
 
-// kept keys of all buckets -> keys[0 .. total), then the bucket counters go back to 0
-__global__ void __launch_bounds__(256)
-by_gather_kernel(const SegView v, unsigned long long* __restrict__ dst, int* __restrict__ total,
-                 int* __restrict__ count) {
-  __shared__ int s_warp[8];
-  __shared__ int s_base;
-  const int seg = blockIdx.x;
+// Global score order of the kept rows of all buckets WITHOUT a sort: every bucket's kept list is
+// already sorted (keys are unique), so the rank of a kept row is its position in its own list
+// plus, for every other bucket, the number of keys below it (one binary search each, the lists
+// are L2-resident).  All SMs work; the single-CTA sort this replaces took 4.4 ms for the 182 k
+// kept rows of the 200 000-candidate case, 0.9 ms for 65 536.  The bucket counters go back to 0.
+constexpr int kRankThreads = 256;
+
+// a warp per kept row (lanes across the buckets); grid sized for the upper bound K kept rows
+__global__ void __launch_bounds__(kRankThreads)
+by_rank_kernel(const SegView v, long long* __restrict__ keep, int* __restrict__ out_K,
+               int* __restrict__ count) {
+  static_assert(kBySegs == kRankThreads, "one thread per bucket");
+  __shared__ int s_off[kBySegs];
+  __shared__ int s_cnt[kBySegs];
+  __shared__ int s_pre[kBySegs + 1];  // exclusive prefix of the kept counts
+  __shared__ int s_warp[kRankThreads / 32];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  int part = 0;
-  for (int i = threadIdx.x; i < seg; i += 256) part += v.kept_count[i];
-  for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
-  if (lane == 0) s_warp[wid] = part;
-  __syncthreads();
-  const int mine = v.kept_count[seg];
-  if (threadIdx.x == 0) {
-    int tot = 0;
-    for (int i = 0; i < 8; ++i) tot += s_warp[i];
-    s_base = tot;
-    if (seg == kBySegs - 1) *total = tot + mine;
-    count[seg] = 0;
+  const int c = v.kept_count[threadIdx.x];
+  s_off[threadIdx.x] = v.seg_off[threadIdx.x];
+  s_cnt[threadIdx.x] = c;
+  int incl = c;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int u = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += u;
   }
+  if (lane == 31) s_warp[wid] = incl;
   __syncthreads();
-  const unsigned long long* kk = v.kept_key + (size_t)v.seg_off[seg];
-  for (int r = threadIdx.x; r < mine; r += 256) dst[s_base + r] = kk[r];
+  int before = 0;
+#pragma unroll
+  for (int k = 0; k < kRankThreads / 32; ++k)
+    if (k < wid) before += s_warp[k];
+  s_pre[threadIdx.x] = before + incl - c;
+  if (threadIdx.x == kRankThreads - 1) s_pre[kBySegs] = before + incl;
+  __syncthreads();
+  const int total = s_pre[kBySegs];
+  if (blockIdx.x == 0) {
+    count[threadIdx.x] = 0;  // candidate counters for the next call
+    if (threadIdx.x == 0) *out_K = total;
+  }
+  const int g = blockIdx.x * (kRankThreads / 32) + wid;  // kept row, in bucket order
+  if (g >= total) return;
+  int lo = 0, hi = kBySegs;  // the bucket: last one whose prefix is <= g
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (s_pre[mid] <= g) lo = mid; else hi = mid;
+  }
+  const int seg = lo, r = g - s_pre[seg];
+  const unsigned long long key = v.kept_key[(size_t)s_off[seg] + r];
+  int part = 0;
+  for (int t = lane; t < kBySegs; t += 32) {
+    const int n = s_cnt[t];
+    if (t == seg || n == 0) continue;
+    const unsigned long long* o = v.kept_key + (size_t)s_off[t];
+    int a = 0, b = n;  // first position whose key is not below `key`
+    while (a < b) {
+      const int mid = (a + b) >> 1;
+      if (__ldg(o + mid) < key) a = mid + 1; else b = mid;
+    }
+    part += a;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+  if (lane == 0) keep[r + part] = (long long)(key & 0xffffffffull);
 }
 
-// one CTA: sort the gathered keys (score descending, row ascending) and write the row indices
-__global__ void __launch_bounds__(kNmsThreads)
-by_final_kernel(unsigned long long* __restrict__ keys, const int* __restrict__ total,
-                long long* __restrict__ keep, int* __restrict__ out_K) {
-  extern __shared__ __align__(16) unsigned long long s_keys[];
-  const int K = *total;
-  sort_keys(keys, K, s_keys);
-  __syncthreads();
-  for (int i = threadIdx.x; i < K; i += kNmsThreads) keep[i] = (long long)(keys[i] & 0xffffffffull);
-  if (threadIdx.x == 0) *out_K = K;
-}
 
 static int next_pow2(long long x) {
   long long p = 1;
@@ -787,7 +816,6 @@ int yh_nms_by_scores(YhWorkspace* ws, const float* ltrb, const float* scores,
     int* by_off = by_count + kBySegs;
     int* by_cursor = by_off + kBySegs + 1;
     int* by_kept = by_cursor + kBySegs;
-    int* by_total = by_kept + kBySegs;
     v.count = by_count;
     v.kept_count = by_kept;
     v.seg_off = by_off;
@@ -806,17 +834,8 @@ int yh_nms_by_scores(YhWorkspace* ws, const float* ltrb, const float* scores,
     int rc = launch_segments(prov, v, kBySegs, iou_threshold, s);
     if (rc) return rc;
     YH_TIME(YH_K_NMS_EMIT, s);
-    by_gather_kernel<<<kBySegs, 256, 0, s>>>(v, ws->cand_key, by_total, by_count);
-    YH_LAUNCHED(s);
-    static bool attr_set = false;  // idempotent; a race only repeats the call
-    const size_t smem = (size_t)kSortTile * sizeof(unsigned long long);
-    if (!attr_set) {
-      YH_CUDA(cudaFuncSetAttribute(by_final_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   (int)smem));
-      attr_set = true;
-    }
-    YH_TIME(YH_K_NMS_EMIT, s);
-    by_final_kernel<<<1, kNmsThreads, smem, s>>>(ws->cand_key, by_total, (long long*)keep, out_K_dev);
+    by_rank_kernel<<<(K + kRankThreads / 32 - 1) / (kRankThreads / 32), kRankThreads, 0, s>>>(
+        v, (long long*)keep, out_K_dev, by_count);
     YH_LAUNCHED(s);
     return YH_OK;
   }
