@@ -569,12 +569,17 @@ pick_kernel(long long* __restrict__ kb, long long* __restrict__ kc, long long* _
 // ---------------------------------------------------------------------------------
 constexpr int kBySegs = 256;
 
+// Group ids are usually small dense integers (batch*C + class, nms.rs:129-133): the low 8 bits
+// taken as they are put up to 256 consecutive ids into 256 DIFFERENT buckets (a random hash of 80
+// ids puts two of them into one bucket for ~11 buckets, and the fullest bucket sets the time);
+// the upper bits are hashed in so that ids that differ by multiples of 256 still spread.
 __device__ __forceinline__ int group_bucket(long long g) {
-  unsigned long long x = (unsigned long long)g;
+  static_assert(kBySegs == 256, "low 8 bits");
+  unsigned long long x = (unsigned long long)g >> 8;
   x ^= x >> 33;
   x *= 0xff51afd7ed558ccdULL;
   x ^= x >> 33;
-  return (int)(x % (unsigned long long)kBySegs);
+  return (int)(((unsigned long long)g ^ x) & 255ull);
 }
 
 __global__ void __launch_bounds__(256)
