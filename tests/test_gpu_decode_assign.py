@@ -161,3 +161,22 @@ def test_assign_csp640_dense_scene_300_gt(dev):
 def test_assign_rejects_bad_threshold(dev):
     with pytest.raises(ValueError, match="anchor_scale_thresh must be greater than or equal to 1"):
         yh.CyCxHWMatcherInit("Rect4", 0.5).build()
+
+
+def test_decode_long_and_thin_maps(dev):
+    """maps longer than the kernel's 1024-entry offset tables (per-element division instead) and
+    planes whose size is not a multiple of 4 / of the 1024-cell chunk"""
+    from yolo_dl_b200.synth import HeadSpec
+    spec = HeadSpec("thin", 64, [(1030, 3), (2, 1500), (1, 1)],
+                    [[(0.1, 0.2), (0.3, 0.1)], [(0.5, 0.4)], [(0.9, 0.8), (0.2, 0.2), (0.4, 0.6)]], 3)
+    B = 2
+    heads_cpu = synth.make_heads(spec, B, 99)
+    heads, detects, merged, infos = build(spec, heads_cpu, dev)
+    ref = odet.forward_merged(heads_cpu, infos, spec.num_classes)
+    for k in ("cy", "cx", "h", "w"):
+        close(getattr(merged, k), ref[k], what=f"thin merged {k}")
+    for l, hc in enumerate(heads_cpu):
+        out = detects[l].forward(heads[l])
+        r = odet.detect2d_forward(hc, spec.num_classes, spec.anchors[l])
+        for k in ("cy", "cx", "h", "w"):
+            close(getattr(out, k), r[k], what=f"thin layer {l} {k}")
