@@ -152,7 +152,8 @@ class DeviceStep:
             pub_done = torch.cuda.Event()
             pub_done.record(self._pub_stream)
         # enqueue the store stream last: the short latency-bound kernels of the other branches then
-        # get their CTAs placed before loss_dense's 2368 CTAs fill every SM (tools/timeline.py)
+        # get their CTAs placed before loss_dense's ~15 400 one-tile CTAs start to stream (tools/timeline.py;
+        # r1f: dense first 195.8 us per step, dense last 193.6)
         dense_last = os.environ.get("YH_DENSE_LAST", "1") == "1"
         if not dense_last:
             _lib.check(self.lib.yh_loss_dense(self.ws.handle, hp, self.layers, self.L, self.B, self.C,
