@@ -132,9 +132,9 @@ def cpu_reference_inputs(sample):
     return spec, heads, odet.make_infos(spec.shapes, spec.anchors), targets
 
 
-def time_cpu_reference(sample, steps, warmup):
+def time_cpu_reference(sample, steps, warmup, threads=None):
     import torch
-    cores = os.cpu_count() or 1
+    cores = threads or os.cpu_count() or 1
     torch.set_num_threads(cores)
     spec, heads, infos, targets = cpu_reference_inputs(sample)
     for _ in range(warmup):
@@ -475,6 +475,12 @@ def run_native(args):
         cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                "sample": f"{args.cpu_sample} images of the same workload, 20 timed passes after 1 warm-up "
                          f"({per:.2f} s/pass)"}
+        # the same path on ONE host thread (the reference's matcher is single-threaded
+        # anyway; this pins the ATen part to one core too): 2 passes of a quarter of the sample
+        q = max(1, args.cpu_sample // 4)
+        v1, per1, _ = time_cpu_reference(q, 2, 1, threads=1)
+        cpu["single_thread"] = {"value": v1, "unit": UNIT, "cores": 1,
+                                "sample": f"{q} images, 2 timed passes after 1 warm-up ({per1:.2f} s/pass)"}
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
