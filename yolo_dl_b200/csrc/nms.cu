@@ -300,7 +300,6 @@ struct SegView {
 // (The first version resolved 32 candidates at a time with a shuffle/ballot loop per candidate
 // and re-tested the later warps after every round: 43 us for ~80 candidates per image.)
 constexpr int kTile = 512;
-constexpr int kStage = 1024;  // kept boxes staged per round (24 KB of the 32 KB bit-matrix area)
 constexpr int kTileWords = kTile / 32;
 constexpr size_t kSegSmem = (size_t)kSortTile * sizeof(unsigned long long) +
                             (size_t)kTile * kTileWords * sizeof(unsigned);
@@ -347,11 +346,10 @@ nms_segment_kernel(const P prov, const SegView v, const double iou_thr) {
     unsigned long long key = 0;
     float4 box = make_float4(0.f, 0.f, 0.f, 0.f);
     long long grp = 0;
-    float area = 0.0f;
     if (alive) {
       key = keys[i];
       prov.get(seg, (unsigned)(key & 0xffffffffull), box, grp);
-      area = box_area(box);
+      const float area = box_area(box);
       const int nc = min(nkept, kKeptCache);
       for (int q = half; q < nc; q += 2) {
         const float4 kb = c_box[q];
@@ -360,29 +358,12 @@ nms_segment_kernel(const P prov, const SegView v, const double iou_thr) {
           break;
         }
       }
-    }
-    // kept boxes beyond the cache: staged through shared memory kStage at a time (the bit
-    // matrix area is free during this step) instead of every thread reading them from the L2:
-    // 65 536 rows of ONE group (30 043 kept) 617 -> 445 ms.  What remains is the ~1 G box tests
-    // themselves on one SM; spreading them over the chip is DESIGN.md §8's first item.
-    {
-      float4* st_box = reinterpret_cast<float4*>(mask);
-      long long* st_grp = reinterpret_cast<long long*>(st_box + kStage);
-      for (int c0 = kKeptCache; c0 < nkept; c0 += kStage) {  // block-uniform
-        const int n = min(kStage, nkept - c0);
-        __syncthreads();
-        for (int j = threadIdx.x; j < n; j += kNmsThreads) {
-          st_box[j] = kept_box[c0 + j];
-          st_grp[j] = kept_grp[c0 + j];
-        }
-        __syncthreads();
-        if (alive) {
-          for (int q = half; q < n; q += 2) {
-            const float4 kb = st_box[q];
-            if (st_grp[q] == grp && suppresses(kb, box_area(kb), box, area, iou_thr)) {
-              alive = false;
-              break;
-            }
+      if (alive) {
+        for (int q = kKeptCache + half; q < nkept; q += 2) {
+          const float4 kb = kept_box[q];
+          if (kept_grp[q] == grp && suppresses(kb, box_area(kb), box, area, iou_thr)) {
+            alive = false;
+            break;
           }
         }
       }
