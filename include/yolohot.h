@@ -112,8 +112,10 @@ int yh_workspace_create(int device, int max_batch, int64_t max_instances,
                         int cand_per_image, YhWorkspace** out);
 int yh_workspace_destroy(YhWorkspace* ws);
 /* Reserves the staging buffer of the matched-row gradients ([capacity, 5+C] f32) that the loss
- * phases use.  The loss calls grow it on demand, but not while their stream is being captured
- * into a CUDA graph (no allocation inside a capture): a capturing caller reserves first. */
+ * phases use when they produce gradients.  This is the ONLY call that grows it (it synchronises
+ * the device and reallocates): the loss entry points never allocate or synchronise, they return
+ * YH_ERR_CAPACITY when `capacity` rows do not fit what was reserved.  Call it from the module
+ * constructor with the largest match capacity (G_max * sum_l A_l * 5), or whenever that grows. */
 int yh_workspace_reserve_rows(YhWorkspace* ws, int capacity, int C);
 const char* yh_last_error(void);
 const char* yh_version(void);
@@ -307,6 +309,14 @@ int yh_inference_pick(YhWorkspace* ws, int64_t* kb, int64_t* kc, int64_t* ki, fl
 int yh_read_counts(YhWorkspace* ws, const int32_t* M_dev, int32_t* M_host,
                    const int32_t* K_dev, int32_t* K_host, void* stream);
 
+/* The reference's candidate filter is `nonzero()`: it takes however many rows pass (nms.rs:97-103).
+ * yh_nms keeps per-image candidate lists of `cand_per_image` entries; the filter keeps COUNTING past
+ * that, so when yh_read_counts reports YH_ERR_CAPACITY (flag 2) this returns the largest per-image
+ * candidate count seen since the previous read (0 if none overflowed): destroy the workspace, create
+ * one with that cand_per_image and call yh_nms again — the count -> allocate -> fill form of
+ * nonzero(), paid only when a batch outgrows the workspace.  Host value, no synchronisation. */
+int yh_workspace_candidates_needed(const YhWorkspace* ws);
+
 /* Number of kernels this library has launched on the calling thread since the last
  * reset (bench.py's `gpu_launches`). */
 int64_t yh_launch_count(int reset);
@@ -315,9 +325,9 @@ int64_t yh_launch_count(int reset);
  * this library is bracketed by a CUDA event pair on its launch stream.  yh_timing_read
  * synchronises on those events and returns, per kernel id (order: decode, assign_slots,
  * assign_emit, loss_dense, loss_rows, nms_filter, nms_segment, nms_emit, nms_pack, pick,
- * benchmark, match_det_gt, ap), the summed device time in ms and the launch count since the last
- * read. */
-#define YH_NUM_KERNELS 13
+ * benchmark, match_det_gt, ap, loss_finish, loss_publish, nms_big), the summed device time in ms
+ * and the launch count since the last read. */
+#define YH_NUM_KERNELS 16
 int yh_timing_enable(int on);
 /* Debug aid: while dev_buf (2 * number-of-kernel-ids uint64, device) is set on this thread, every
  * launch is bracketed by one-thread kernels that write %globaltimer (ns) to dev_buf[2*id] and

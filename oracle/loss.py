@@ -70,8 +70,11 @@ def _cross_entropy(inp, target_dense, reduction):
     sparse = target_dense.max(dim=1)[1]
     if inp.numel() == 0 and reduction == "mean":
         return torch.zeros((), dtype=torch.float32, device=inp.device)
-    loss = F.nll_loss(F.log_softmax(inp, dim=-1), sparse, reduction="none")
-    return _reduce(loss, reduction)
+    # tch 0.7 `cross_entropy_for_logits` = log_softmax(-1).nll_loss(target) and `nll_loss` is the
+    # generated wrapper with Reduction::Mean: ALREADY a scalar mean over the rows, so the
+    # .sum() / .mean() of cross_entropy.rs:47-51 change nothing (M = 0 with Sum: NaN, like ATen)
+    loss = F.nll_loss(F.log_softmax(inp, dim=-1), sparse, reduction="mean")
+    return loss if reduction == "none" else _reduce(loss, reduction)
 
 
 def _kind_loss(kind, inp, target, pos_weight, gamma, reduction):

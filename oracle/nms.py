@@ -83,6 +83,12 @@ def nms_forward(merged: dict, conf_thr: float, iou_thr: float, by_class: bool,
         K = batches.shape[0]
         ltrb = torch.cat([new_l, new_t, new_r, new_b], 1)
         group = batches * C + classes if by_class else batches.clone()
+        # everything up to here is the reference's ATen op sequence and runs on whatever device
+        # `merged` lives on (CPU, or CUDA = the reference's real deployment through libtorch);
+        # the greedy stand-in for tch-nms below works on host copies of its inputs
+        tlbr_t = torch.cat([new_t, new_l, new_b, new_r], 1).cpu()
+        ltrb, conf, group = ltrb.cpu(), conf.cpu(), group.cpu()
+        batches, classes, instances = batches.cpu(), classes.cpu(), instances.cpu()
         if K == 0:
             keep = np.zeros(0, dtype=np.int64)
         else:
@@ -106,10 +112,11 @@ def nms_forward(merged: dict, conf_thr: float, iou_thr: float, by_class: bool,
         N = merged["cy"].shape[2]
         order = np.lexsort((kc * N + ki, -kconf.astype(np.float64), kb))
         keep = keep[order]
-        tlbr = torch.cat([new_t, new_l, new_b, new_r], 1).numpy()
+        tlbr = tlbr_t.numpy()
         return dict(batches=batches.numpy()[keep], classes=classes.numpy()[keep],
                     instances=instances.numpy()[keep], tlbr=tlbr[keep],
-                    conf=conf.view(-1).numpy()[keep], num_candidates=K)
+                    conf=conf.view(-1).numpy()[keep], num_candidates=K,
+                    cand=(batches.numpy(), classes.numpy(), instances.numpy()))
 
 
 def inference_pick(out: dict):

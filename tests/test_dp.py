@@ -97,3 +97,27 @@ def test_single_process_is_a_local_scale():
     assert all(bool((p.grad == 1.0).all()) for p in params)
     gar.zero_grad()
     assert all(bool((p.grad == 0.0).all()) for p in params)
+
+
+def test_reduce_repairs_grads_dropped_by_set_to_none():
+    """optimizer.zero_grad(set_to_none=True) drops the bucket views; the next backward allocates
+    fresh .grad tensors.  reduce() must pick those up (and re-point .grad at the buckets) instead
+    of averaging stale zero buckets."""
+    sys.path.insert(0, ROOT)
+    from yolo_dl_b200 import dp
+    params = _make_params(2)
+    gar = dp.GradientAllReduce(params)
+    opt = torch.optim.SGD(params, lr=0.1)
+    opt.zero_grad(set_to_none=True)
+    assert all(p.grad is None for p in params)
+    sum((p * p).sum() for p in params[:-1]).backward()     # the last parameter gets no gradient
+    want = [2.0 * p.detach() * 0.5 for p in params[:-1]]
+    gar.reduce(4, 8)
+    for p, w in zip(params[:-1], want):
+        assert torch.equal(p.grad, w)
+    assert bool((params[-1].grad == 0).all())
+    ptrs = {b.data_ptr() for b in gar.buckets}
+    assert all(p.grad.data_ptr() in range(min(ptrs), max(ptrs) + gar.nbytes()) for p in params)
+    gar.zero_grad()
+    sum((p * p).sum() for p in params).backward()
+    assert torch.equal(gar._views[0], params[0].grad)      # accumulates straight into the bucket

@@ -86,9 +86,19 @@ def test_nms_candidate_overflow_is_reported(dev):
     spec = synth.small_spec()
     heads_cpu = synth.make_heads(spec, 2, 5, obj_mean=3.0, cls_mean=3.0)
     _, _, merged, _ = build(spec, heads_cpu, dev)
-    nms = yh.NonMaxSuppressionInit(0.5, 0.1, False, max_candidates_per_image=64).build()
-    with pytest.raises(yh.YoloHotError, match="overflow"):
+    nms = yh.NonMaxSuppressionInit(0.5, 0.1, False, max_candidates_per_image=64, grow=False).build()
+    with pytest.raises(yh.YoloHotError, match="overflow") as e:
         nms.forward(merged)
+    assert e.value.status == yh._lib.YH_ERR_CAPACITY
+    # the filter counted past the capacity: the host learns how much room the batch needs
+    need = yh.load().yh_workspace_candidates_needed(nms._ws.handle)
+    assert need > 64
+    # ... and with `grow` (the default) the same call succeeds: count -> allocate -> fill
+    grown = yh.NonMaxSuppressionInit(0.5, 0.1, False, max_candidates_per_image=64).build()
+    out = grown.forward(merged)
+    assert grown.max_candidates_per_image >= need
+    big = yh.NonMaxSuppressionInit(0.5, 0.1, False, max_candidates_per_image=1 << 16).build().forward(merged)
+    assert torch.equal(out.instances, big.instances) and torch.equal(out.batches, big.batches)
 
 
 @pytest.mark.parametrize("K", [0, 1, 2, 33, 1000, 5000, 8192, 8193, 20000, 65536, 70000])
@@ -117,7 +127,7 @@ def test_nms_by_scores_matches_torchvision(dev):
     assert np.array_equal(got.cpu().numpy(), ref)
 
 
-@pytest.mark.parametrize("K,groups", [(100000, 80), (200000, 80), (100000, 4)])
+@pytest.mark.parametrize("K,groups", [(100000, 80), (200000, 80), (100000, 4), (65536, 1), (200000, 1)])
 def test_nms_sweep_100k_200k(dev, K, groups):
     """BASELINE config 4, the sizes above one 65 536-row chunk: one global NMS over all rows,
     checked against torchvision's batched_nms (C++ on the host; the numpy oracle is O(K*kept))."""

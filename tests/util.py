@@ -32,6 +32,19 @@ def grad_close(a, b, what=""):
     close(a, b_, rtol=RTOL, atol=RTOL * float(b_.abs().max()) + 1e-12, what=what)
 
 
+def grad_report(a, b, floor=1e-3):
+    """(worst element-wise relative error over the elements with |b| >= floor*max|b|,
+    max|a-b| / max|b|) of a gradient tensor against its reference."""
+    a = torch.as_tensor(a).detach().cpu().double().flatten()
+    b = torch.as_tensor(b).detach().cpu().double().flatten()
+    mx = float(b.abs().max())
+    if mx == 0.0:
+        return 0.0, float((a - b).abs().max())
+    sig = b.abs() >= floor * mx
+    err = (a - b).abs()
+    return float((err[sig] / b.abs()[sig]).max()), float(err.max()) / mx
+
+
 def build(spec, heads_cpu, dev, requires_grad=False):
     heads = [h.to(dev).requires_grad_(requires_grad) for h in heads_cpu]
     detects = [yh.Detect2DInit(spec.num_classes, a).build() for a in spec.anchors]

@@ -92,6 +92,7 @@ SYMBOLS = {
     "yh_loss_collect": (c_int, [c_void_p, POINTER(c_float), POINTER(ctypes.c_uint32), c_void_p]),
     "yh_read_counts": (c_int, [c_void_p, c_void_p, POINTER(c_int32), c_void_p, POINTER(c_int32),
                                c_void_p]),
+    "yh_workspace_candidates_needed": (c_int, [c_void_p]),
     "yh_launch_count": (c_int64, [c_int]),
     "yh_timing_enable": (c_int, [c_int]),
     "yh_trace_enable": (c_int, [c_void_p]),
@@ -101,7 +102,8 @@ SYMBOLS = {
 KERNEL_NAMES = ["decode_kernel", "assign_slots_kernel", "assign_emit_kernel", "loss_dense_kernel",
                 "loss_rows_kernel", "nms_filter_kernel", "nms_segment_kernel", "nms_emit_kernel",
                 "nms_pack_kernel", "pick_kernel", "benchmark_kernel",
-                "match_det_gt_kernel", "ap_kernel", "loss_finish_kernel", "loss_publish_kernel"]
+                "match_det_gt_kernel", "ap_kernel", "loss_finish_kernel", "loss_publish_kernel",
+                "nms_big_kernel"]
 
 _lib = None
 

@@ -124,7 +124,9 @@ extern "C" int yh_benchmark(YhWorkspace* ws, const float* const* heads, const Yh
   YH_REQUIRE(ws != nullptr, "workspace is NULL");
   YH_REQUIRE(counts5_dev != nullptr && M_dev != nullptr, "NULL argument");
   YH_REQUIRE(capacity == 0 || (pred_rows_dev && m_class), "matched rows are NULL");
-  YH_REQUIRE(B >= 1, "B=%d", B);
+  YH_REQUIRE(heads != nullptr, "heads is NULL");
+  YH_REQUIRE(capacity >= 0, "capacity=%d", capacity);
+  YH_REQUIRE(B >= 1 && B <= ws->max_batch, "B=%d outside 1..max_batch=%d", B, ws->max_batch);
   LayerTab tab;
   int rc = build_layer_tab(layers, L, C, heads, &tab);
   if (rc) return rc;

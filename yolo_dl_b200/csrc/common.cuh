@@ -43,7 +43,7 @@ int64_t& launch_counter();
 enum KernelId {
   YH_K_DECODE = 0, YH_K_ASSIGN_SLOTS, YH_K_ASSIGN_EMIT, YH_K_LOSS_DENSE, YH_K_LOSS_ROWS,
   YH_K_NMS_FILTER, YH_K_NMS_SEGMENT, YH_K_NMS_EMIT, YH_K_NMS_PACK, YH_K_PICK, YH_K_BENCHMARK,
-  YH_K_MATCH_DET_GT, YH_K_AP, YH_K_LOSS_FINISH, YH_K_LOSS_PUBLISH, YH_K_COUNT
+  YH_K_MATCH_DET_GT, YH_K_AP, YH_K_LOSS_FINISH, YH_K_LOSS_PUBLISH, YH_K_NMS_BIG, YH_K_COUNT
 };
 void timing_begin(int id, cudaStream_t s);  // no-ops unless timing is enabled on this thread
 void timing_end(cudaStream_t s);
@@ -77,9 +77,9 @@ struct LayerTab {
 int build_layer_tab(const YhLayer* layers, int L, int C, const float* const* heads,
                     LayerTab* tab);
 
-// Grows ws->row_grad to `floats` (no-op when large enough).  Allocation is not possible while
-// `s` is being captured into a CUDA graph: reserve first (yh_workspace_reserve_rows).
-int reserve_rows(YhWorkspace* ws, size_t floats, cudaStream_t s);
+// Grows ws->row_grad to `floats` (no-op when large enough).  Only yh_workspace_reserve_rows calls
+// it: it synchronises the device and reallocates, which no compute entry point may do.
+int reserve_rows(YhWorkspace* ws, size_t floats);
 
 // Position of a flat instance index inside its layer.
 struct Cell {
@@ -178,8 +178,18 @@ struct YhWorkspace {
 
   int* by_ints;                   // yh_nms_by_scores buckets: count | off | cursor | kept | total
 
+  // nms_big_kernel (segments above YH_BIG_MIN candidates); allocated when cand_per_image > YH_BIG_MIN
+  float4* big_box;                // [8 groups * big_len] boxes of the segment a CTA group works on
+  long long* big_grp;             // [8 groups * big_len]
+  long long big_len;              // = cand_stride
+  unsigned* big_sync;             // barrier counters | cross-test masks | kept counts (YH_BIG_SYNC_WORDS)
+  int* cand_need;                 // device: largest candidate count that exceeded the capacity
+  int cand_need_host;             // its value at the last yh_read_counts
+
   int* err_flag;                  // device: sticky overflow flag
   int32_t* host_counts;           // pinned, [max_batch + 8]
 };
 
 #define YH_PARTIALS_MAX 8192
+#define YH_BIG_MIN 4096          // candidates per segment above which the multi-CTA NMS kernel takes it
+#define YH_BIG_SYNC_WORDS 1024

@@ -116,16 +116,8 @@ int build_layer_tab(const YhLayer* layers, int L, int C, const float* const* hea
   return YH_OK;
 }
 
-int reserve_rows(YhWorkspace* ws, size_t floats, cudaStream_t s) {
+int reserve_rows(YhWorkspace* ws, size_t floats) {
   if (floats <= ws->row_grad_floats) return YH_OK;
-  cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
-  if (cudaStreamIsCapturing(s, &st) != cudaSuccess) {
-    cudaGetLastError();
-    st = cudaStreamCaptureStatusNone;
-  }
-  YH_REQUIRE(st == cudaStreamCaptureStatusNone,
-             "row-gradient staging (%zu floats) must be reserved before stream capture: call "
-             "yh_workspace_reserve_rows(ws, capacity, C) first", floats);
   YH_CUDA(cudaSetDevice(ws->device));
   // the old buffer may still be in use by work already enqueued on this device
   YH_CUDA(cudaDeviceSynchronize());
@@ -144,12 +136,12 @@ extern "C" {
 int yh_workspace_reserve_rows(YhWorkspace* ws, int capacity, int C) {
   YH_REQUIRE(ws != nullptr, "workspace is NULL");
   YH_REQUIRE(capacity >= 0 && C >= 1, "capacity=%d C=%d", capacity, C);
-  return yh::reserve_rows(ws, (size_t)capacity * (size_t)(5 + C), nullptr);
+  return yh::reserve_rows(ws, (size_t)capacity * (size_t)(5 + C));
 }
 
 const char* yh_last_error(void) { return yh::g_err; }
 
-const char* yh_version(void) { return "yolohot 0.1 (sm_100a)"; }
+const char* yh_version(void) { return "yolohot 0.2 (sm_100a)"; }
 
 int64_t yh_launch_count(int reset) {
   int64_t v = yh::g_launches;
@@ -208,6 +200,10 @@ int yh_workspace_destroy(YhWorkspace* ws) {
   cudaFree(ws->kept_count);
   cudaFree(ws->kept_grp);
   cudaFree(ws->by_ints);
+  cudaFree(ws->big_box);
+  cudaFree(ws->big_grp);
+  cudaFree(ws->big_sync);
+  cudaFree(ws->cand_need);
   cudaFree(ws->err_flag);
   if (ws->host_counts) cudaFreeHost(ws->host_counts);
   delete ws;
@@ -275,6 +271,14 @@ int yh_workspace_create(int device, int max_batch, int64_t max_instances, int ca
   YH_ALLOC(ws->kept_count, (size_t)max_batch * sizeof(int));
   YH_ALLOC(ws->kept_grp, cands * sizeof(long long));
   YH_ALLOC(ws->by_ints, 2048 * sizeof(int));
+  YH_ALLOC(ws->cand_need, 64);
+  if (cand_per_image > YH_BIG_MIN) {
+    // staging of the multi-CTA NMS kernel: 8 CTA groups, each working on one big segment
+    ws->big_len = ws->cand_stride;
+    YH_ALLOC(ws->big_box, (size_t)8 * (size_t)ws->big_len * sizeof(float4));
+    YH_ALLOC(ws->big_grp, (size_t)8 * (size_t)ws->big_len * sizeof(long long));
+    YH_ALLOC(ws->big_sync, YH_BIG_SYNC_WORDS * sizeof(unsigned));
+  }
   YH_ALLOC(ws->err_flag, 64);
 #undef YH_ALLOC
   // the matcher's slot table is EMPTY between calls (assign.cu)
@@ -283,6 +287,7 @@ int yh_workspace_create(int device, int max_batch, int64_t max_instances, int ca
       cudaMemset(ws->cand_count, 0, (size_t)max_batch * sizeof(int)) != cudaSuccess ||
       cudaMemset(ws->by_ints, 0, 2048 * sizeof(int)) != cudaSuccess ||
       cudaMemset(ws->ticket, 0, 64) != cudaSuccess ||
+      cudaMemset(ws->cand_need, 0, 64) != cudaSuccess ||
       cudaMemset(ws->err_flag, 0, 64) != cudaSuccess ||
       cudaMallocHost((void**)&ws->host_counts, ((size_t)max_batch + 8) * sizeof(int32_t)) !=
           cudaSuccess) {
@@ -294,18 +299,25 @@ int yh_workspace_create(int device, int max_batch, int64_t max_instances, int ca
   return YH_OK;
 }
 
+int yh_workspace_candidates_needed(const YhWorkspace* ws) {
+  return ws ? ws->cand_need_host : 0;
+}
+
 int yh_read_counts(YhWorkspace* ws, const int32_t* M_dev, int32_t* M_host, const int32_t* K_dev,
                    int32_t* K_host, void* stream) {
   YH_REQUIRE(ws != nullptr, "workspace is NULL");
   cudaStream_t s = (cudaStream_t)stream;
   YH_CUDA(cudaSetDevice(ws->device));
   int32_t* h = ws->host_counts;
-  h[0] = h[1] = h[2] = 0;
+  h[0] = h[1] = h[2] = h[3] = 0;
   if (M_dev) YH_CUDA(cudaMemcpyAsync(&h[0], M_dev, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
   if (K_dev) YH_CUDA(cudaMemcpyAsync(&h[1], K_dev, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
   YH_CUDA(cudaMemcpyAsync(&h[2], ws->err_flag, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
   YH_CUDA(cudaMemsetAsync(ws->err_flag, 0, sizeof(int32_t), s));
+  YH_CUDA(cudaMemcpyAsync(&h[3], ws->cand_need, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+  YH_CUDA(cudaMemsetAsync(ws->cand_need, 0, sizeof(int32_t), s));
   YH_CUDA(cudaStreamSynchronize(s));
+  ws->cand_need_host = h[3];
   if (M_host) *M_host = h[0];
   if (K_host) *K_host = h[1];
   if (h[2] & 8) {
@@ -314,9 +326,10 @@ int yh_read_counts(YhWorkspace* ws, const int32_t* M_dev, int32_t* M_host, const
     return YH_ERR_INVALID;
   }
   if (h[2] != 0) {
-    yh::set_error("a device buffer overflowed (flag=%d): 1=matches, 2=nms candidates, "
-                  "4=nms outputs",
-                  h[2]);
+    yh::set_error("a device buffer overflowed (flag=%d): 1=matches, 2=nms candidates (largest image "
+                  "had %d, cand_per_image=%d: recreate the workspace with "
+                  "yh_workspace_candidates_needed), 4=nms outputs",
+                  h[2], h[3], ws->cand_per_image);
     return YH_ERR_CAPACITY;
   }
   return YH_OK;

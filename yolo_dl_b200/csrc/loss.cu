@@ -667,7 +667,10 @@ loss_rows_kernel(const LayerTab t, const LossParams p,
         } else if (p.cls_kind == YH_LOSS_CROSS_ENTROPY) {
           if (k == ce_t) bce += lse - x;
           gi = expf(x - lse) - (k == ce_t ? 1.0f : 0.0f);
-          if (p.reduction == YH_REDUCTION_MEAN) gi = gi / Mf;  // mean over the M rows
+          // tch 0.7's cross_entropy_for_logits is log_softmax + nll_loss with nll_loss's DEFAULT
+          // Mean reduction: already a scalar mean over the M rows, which cross_entropy.rs:47-51's
+          // .sum() / .mean() leave unchanged — 1/M for BOTH reductions
+          gi = gi / Mf;
         } else {
           bce += kind_loss(p.cls_kind, x, tt, false, 0.0f, p.gamma, gi);
           if (p.reduction == YH_REDUCTION_MEAN) gi = gi / MCf;
@@ -850,7 +853,9 @@ loss_finish_kernel(const LayerTab t, const GradTab g, const LossParams p,
       obj_l = (float)(obj_sum / ((double)p.B * (double)t.N));
     } else {
       iou_l = (float)iou_sum;
-      cls_l = (float)cls_sum;
+      // CrossEntropy: nll_loss's own Mean reduction has already happened (see loss_rows_kernel);
+      // M = 0 gives the mean of an empty tensor, NaN, exactly as cross_entropy.rs:41-51 does
+      cls_l = (p.cls_kind == YH_LOSS_CROSS_ENTROPY) ? (float)(cls_sum / (double)M) : (float)cls_sum;
       obj_l = (float)obj_sum;
     }
     // loss_.rs:258-260, f32 tensor arithmetic with f32-cast scalars
@@ -995,9 +1000,13 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
   if (row_grid < 1) row_grid = 1;
   if (row_grid > kPartHalf) row_grid = kPartHalf;
   const bool want_grad = grad_heads != nullptr || want_grad_rows != 0;
-  if (want_grad && (phases & (kPhaseRows | kPhaseFinish)) && capacity > 0) {
-    rc = reserve_rows(ws, (size_t)capacity * (size_t)tab.E, s);
-    if (rc) return rc;
+  if (want_grad && (phases & (kPhaseRows | kPhaseFinish)) && capacity > 0 &&
+      (size_t)capacity * (size_t)tab.E > ws->row_grad_floats) {
+    // no allocation and no synchronisation inside a compute entry point (yolohot.h conventions)
+    set_error("row-gradient staging holds %zu floats, capacity=%d rows of %d need %zu: call "
+              "yh_workspace_reserve_rows(ws, capacity, C) first",
+              ws->row_grad_floats, capacity, tab.E, (size_t)capacity * (size_t)tab.E);
+    return YH_ERR_CAPACITY;
   }
   if (phases & kPhaseRows) {
     YH_TIME(YH_K_LOSS_ROWS, s);

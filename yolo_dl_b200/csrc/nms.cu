@@ -23,11 +23,18 @@
 //                       Per-class suppression only adds "same class" to the predicate, so one
 //                       sorted list per image serves both modes (nms.rs:129-133).
 //   nms_emit_kernel     ordered compaction of the per-image kept lists into the outputs.
+//   nms_big_kernel      segments (an image; a group bucket of yh_nms_by_scores) with more than
+//                       kBigMin candidates: the same greedy pass spread over ALL SMs — merge sort,
+//                       box gather, and per 512-candidate tile the test against the kept list on
+//                       every SM but one, which resolves the previous tile meanwhile.  Per-image
+//                       groups (`suppress_by_class: false`) are the only mode the reference's
+//                       binaries use (train/src/train/multi_gpu.rs:72, single_gpu.rs:59,
+//                       detect/src/main.rs:84), so one big group must not sit on one SM.
 // yh_nms_by_scores exposes the same engine on explicit [K,4] ltrb boxes / scores / int64 groups,
 // i.e. the drop-in for tch_nms::nms_by_scores itself.
 #include <math.h>
-
 #include <stdlib.h>
+#include <string.h>
 
 #include "common.cuh"
 
@@ -285,6 +292,8 @@ struct SegView {
   long long stride;
   int cap;
   const int* seg_off;            // optional: segment s starts at seg_off[s] instead of s*stride
+  int* need;                     // atomicMax of the candidate counts that exceeded cap
+  int big_min;                   // segments with more candidates belong to nms_big_kernel (0: none do)
 };
 
 // Greedy pass, in tiles of kTile candidates (score order):
@@ -316,7 +325,11 @@ nms_segment_kernel(const P prov, const SegView v, const double iou_thr) {
 
   const int seg = blockIdx.x;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  const int K = min(v.count[seg], v.cap);
+  const int found = v.count[seg];  // reset to 0 by the emit / rank kernel that follows
+  const int K = min(found, v.cap);
+  // the filter keeps counting past the capacity: tell the host how much room the caller needs
+  if (threadIdx.x == 0 && found > v.cap) atomicMax(v.need, found);
+  if (v.big_min > 0 && K > v.big_min) return;  // nms_big_kernel's (all threads: block-uniform)
   const size_t seg_base = v.seg_off ? (size_t)v.seg_off[seg] : (size_t)seg * (size_t)v.stride;
   unsigned long long* keys = v.keys + seg_base;
   unsigned long long* kept_key = v.kept_key + seg_base;
@@ -325,9 +338,6 @@ nms_segment_kernel(const P prov, const SegView v, const double iou_thr) {
 
   sort_keys(keys, K, s_keys);
   __syncthreads();
-  // every thread has read the count: leave it 0 for the next filter pass (the per-call memset
-  // node this replaces sat behind the dense store stream in the overlapped step)
-  if (threadIdx.x == 0) v.count[seg] = 0;
 
   // the sort tile becomes the kept-box cache; the bit matrix lives behind it
   float4* c_box = reinterpret_cast<float4*>(s_keys);
@@ -442,6 +452,362 @@ nms_segment_kernel(const P prov, const SegView v, const double iou_thr) {
   if (threadIdx.x == 0) v.kept_count[seg] = nkept;
 }
 
+
+// ---------------------------------------------------------------------------------
+// sort + greedy NMS of LARGE segments on all SMs
+// ---------------------------------------------------------------------------------
+// One persistent cooperative launch (one CTA per SM) handles every segment with more than
+// kBigMin candidates.  The grid splits into up to kBigGroups groups of CTAs, each with its own
+// barrier, and the big segments are dealt round-robin to the groups (B = 8 images of 200 000
+// candidates run as 8 concurrent groups of 18 SMs; one segment gets all SMs).  Per segment:
+//   1. merge sort: every CTA sorts tiles of 8192 keys in shared memory, then log2(tiles) merge
+//      passes, each output chunk of 8192 located by a merge-path binary search, loaded as a
+//      bitonic sequence (A ascending ++ B descending) and merged in shared memory;
+//   2. gather: the (t,l,b,r) box and group of every candidate in sorted order, once, into a
+//      per-group staging buffer (the head-reading provider decodes them; 148 CTAs re-decoding
+//      every tile would cost more than the tests);
+//   3. greedy pass in tiles of 512, software-pipelined over the group barrier: in phase p
+//        * CTAs 1.. of the group test tile p+1 against the boxes kept by tiles < p (kept list
+//          split evenly over the CTAs, two threads per candidate, results OR-ed into a 512-bit
+//          mask with one atomicOr per warp);
+//        * CTA 0 resolves tile p: mask from phase p-1, test against the boxes tile p-1 kept
+//          (still in its shared memory), 512 x 512 suppression bit matrix, in-order walk by one
+//          warp, append — the only serial part, ~20 us per tile of survivors, far less when
+//          most of the tile is already suppressed.
+// 65 536 candidates of ONE group: 617 ms on one CTA (round 1) -> a few ms.
+constexpr int kBigThreads = 1024;
+constexpr int kBigMin = YH_BIG_MIN;
+constexpr int kBigGroups = 8;
+constexpr int kStage = 2048;  // kept boxes a tester CTA stages in shared memory per round (48 KB)
+
+struct BigView {
+  float4* box;        // [kBigGroups * len] boxes of the segment a group is working on, sorted order
+  long long* grp;     // [kBigGroups * len]
+  long long len;
+  unsigned* sync;     // [kBigGroups * 32] barrier counters, zero at launch
+  unsigned* dead;     // [kBigGroups * 2 * kTileWords] cross-test masks, zero at launch
+  int* nkept;         // [kBigGroups * 2] kept count as of the start of a phase (double-buffered)
+};
+
+// barrier of the n CTAs of a group: a monotonically increasing arrival counter
+__device__ __forceinline__ void group_sync(unsigned* ctr, unsigned& target, const unsigned n) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    target += n;
+    __threadfence();
+    atomicAdd(ctr, 1u);
+    unsigned seen;
+    do {
+      asm volatile("ld.acquire.gpu.u32 %0, [%1];" : "=r"(seen) : "l"(ctr) : "memory");
+    } while (seen < target);
+  }
+  __syncthreads();
+}
+
+// ascending bitonic merge of the bitonic sequence s[0..kSortTile)
+__device__ __forceinline__ void smem_merge_asc(unsigned long long* s) {
+  for (int j = kSortTile >> 1; j >= 1; j >>= 1) {
+    for (int p = threadIdx.x; p < kSortTile / 2; p += kBigThreads) {
+      const int i = ((p & ~(j - 1)) << 1) | (p & (j - 1));
+      const int l = i | j;
+      const unsigned long long a = s[i], c = s[l];
+      if (a > c) {
+        s[i] = c;
+        s[l] = a;
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// merge path: how many of the first `diag` outputs of merge(A[0..nA), B[0..nB)) come from A
+__device__ __forceinline__ int merge_path(const unsigned long long* __restrict__ A, const int nA,
+                                          const unsigned long long* __restrict__ B, const int nB,
+                                          const int diag) {
+  int lo = max(0, diag - nB), hi = min(diag, nA);
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (__ldcg(A + mid) < __ldcg(B + (diag - 1 - mid))) lo = mid + 1; else hi = mid;
+  }
+  return lo;
+}
+
+template <class P>
+__global__ void __launch_bounds__(kBigThreads)
+nms_big_kernel(const P prov, const SegView v, const int S, const BigView big,
+               const double iou_thr) {
+  extern __shared__ __align__(16) unsigned long long s_keys[];
+  __shared__ float4 t_box[kTile];
+  __shared__ long long t_grp[kTile];
+  __shared__ unsigned s_al[2][kTileWords];
+  __shared__ unsigned s_keep[32];
+  __shared__ int s_list[kBigThreads];
+  __shared__ int s_scan[kBigThreads / 32];
+  __shared__ int s_split[2];
+  static_assert(kBigThreads == 2 * kTile, "two threads per candidate of a tile");
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+
+  // ---- which segments are big, and how the grid splits -------------------------------------
+  int nbig = 0;
+  for (int i = threadIdx.x; i < S; i += kBigThreads) nbig += min(v.count[i], v.cap) > v.big_min;
+  for (int o = 16; o > 0; o >>= 1) nbig += __shfl_xor_sync(0xffffffffu, nbig, o);
+  if (lane == 0) s_scan[wid] = nbig;
+  __syncthreads();
+  nbig = 0;
+  for (int k = 0; k < kBigThreads / 32; ++k) nbig += s_scan[k];
+  __syncthreads();
+  if (nbig == 0) return;
+  const int G = (int)gridDim.x;
+  int ngroups = min(min(nbig, kBigGroups), max(G / 2, 1));
+  const int csz = G / ngroups;              // CTAs per group
+  const int g = (int)blockIdx.x / csz;      // my group
+  const int r = (int)blockIdx.x - g * csz;  // my rank inside it
+  if (g >= ngroups) return;                 // left-over CTAs
+  unsigned* ctr = big.sync + g * 32;
+  unsigned target = 0;
+  float4* bbox = big.box + (size_t)g * (size_t)big.len;
+  long long* bgrp = big.grp + (size_t)g * (size_t)big.len;
+  unsigned* dead = big.dead + g * 2 * kTileWords;
+  int* nk_pub = big.nkept + g * 2;
+
+  int seen = 0;  // big segments before the current chunk
+  for (int chunk = 0; chunk < S; chunk += kBigThreads) {
+    // big segments of this chunk, in order; mine are those whose rank % ngroups == g
+    const int si = chunk + threadIdx.x;
+    const bool isbig = si < S && min(v.count[si], v.cap) > v.big_min;
+    const unsigned bm = __ballot_sync(0xffffffffu, isbig);
+    if (lane == 0) s_scan[wid] = __popc(bm);
+    __syncthreads();
+    int before = 0, total = 0;
+    for (int k = 0; k < kBigThreads / 32; ++k) {
+      if (k < wid) before += s_scan[k];
+      total += s_scan[k];
+    }
+    const int rank = seen + before + __popc(bm & ((1u << lane) - 1u));
+    // compact my group's segments: position = (rank - first rank of mine in this chunk) / ngroups
+    const int first = ((g - seen) % ngroups + ngroups) % ngroups;  // chunk-local rank of my first
+    if (isbig && rank % ngroups == g) s_list[(rank - seen - first) / ngroups] = si;
+    const int nmine = (total > first) ? (total - first + ngroups - 1) / ngroups : 0;
+    __syncthreads();
+    seen += total;
+
+    for (int li = 0; li < nmine; ++li) {
+      const int seg = s_list[li];
+      const int K = min(v.count[seg], v.cap);
+      const size_t seg_base = v.seg_off ? (size_t)v.seg_off[seg] : (size_t)seg * (size_t)v.stride;
+      unsigned long long* keys = v.keys + seg_base;
+      unsigned long long* kept_key = v.kept_key + seg_base;
+      float4* kept_box = v.kept_box + seg_base;
+      long long* kept_grp = v.kept_grp + seg_base;
+
+      // ---- 1. merge sort (result in `keys`) -------------------------------------------------
+      const int ntile = (K + kSortTile - 1) / kSortTile;
+      const int Kp = ntile * kSortTile;  // the segment has room for it: power-of-two >= 8192
+      int npass = 0;
+      for (int run = 1; run < ntile; run <<= 1) ++npass;
+      unsigned long long* src = (npass & 1) ? kept_key : keys;
+      unsigned long long* dst = (npass & 1) ? keys : kept_key;
+      for (int t = r; t < ntile; t += csz) {
+        const int base = t * kSortTile;
+        for (int i = threadIdx.x; i < kSortTile; i += kBigThreads)
+          s_keys[i] = (base + i < K) ? keys[base + i] : ~0ull;
+        __syncthreads();
+        for (int k = 2; k <= kSortTile; k <<= 1) smem_passes(s_keys, kSortTile, 0, k, k >> 1);
+        for (int i = threadIdx.x; i < kSortTile; i += kBigThreads) src[base + i] = s_keys[i];
+        __syncthreads();
+      }
+      group_sync(ctr, target, csz);
+      for (int run = kSortTile; run < Kp; run <<= 1) {
+        for (int c = r; c < ntile; c += csz) {
+          const int obase = c * kSortTile;
+          const int pbase = obase / (2 * run) * (2 * run);
+          const unsigned long long* A = src + pbase;
+          const int nA = min(run, Kp - pbase);
+          const unsigned long long* Bq = A + nA;
+          const int nB = min(run, Kp - pbase - nA);
+          const int diag = obase - pbase;
+          if (threadIdx.x < 2) s_split[threadIdx.x] = merge_path(A, nA, Bq, nB, diag + threadIdx.x * kSortTile);
+          __syncthreads();
+          const int a0 = s_split[0], a1 = s_split[1];
+          const int b0 = diag - a0, na = a1 - a0;
+          for (int i = threadIdx.x; i < kSortTile; i += kBigThreads)
+            s_keys[i] = (i < na) ? __ldcg(A + a0 + i) : __ldcg(Bq + b0 + (kSortTile - 1 - i));
+          __syncthreads();
+          smem_merge_asc(s_keys);
+          for (int i = threadIdx.x; i < kSortTile; i += kBigThreads) dst[obase + i] = s_keys[i];
+          __syncthreads();
+        }
+        group_sync(ctr, target, csz);
+        unsigned long long* tmp = src;
+        src = dst;
+        dst = tmp;
+      }
+      // ---- 2. gather the boxes in sorted order ----------------------------------------------
+      for (int i = r * kBigThreads + threadIdx.x; i < K; i += csz * kBigThreads) {
+        float4 box;
+        long long grp;
+        prov.get(seg, (unsigned)(__ldcg(keys + i) & 0xffffffffull), box, grp);
+        bbox[i] = box;
+        bgrp[i] = grp;
+      }
+      if (r == 0 && threadIdx.x < 2) nk_pub[threadIdx.x] = 0;
+      group_sync(ctr, target, csz);
+
+      // ---- 3. greedy pass, pipelined over tiles ---------------------------------------------
+      const int ntiles = (K + kTile - 1) / kTile;
+      const int ti = threadIdx.x & (kTile - 1);
+      const int half = threadIdx.x >> 9;
+      unsigned* mask = reinterpret_cast<unsigned*>(s_keys);                  // 32 KB
+      float4* p_box = reinterpret_cast<float4*>(mask + kTile * kTileWords);  // 8 KB: previous tile's kept
+      long long* p_grp = reinterpret_cast<long long*>(p_box + kTile);        // 4 KB
+      int nkept = 0, npk = 0;
+      for (int p = 0; p < ntiles; ++p) {
+        if (r == 0 || csz == 1) {
+          // resolver: tile p
+          const int base = p * kTile;
+          const int nt = min(K - base, kTile);
+          const int nwords = (nt + 31) >> 5;
+          bool alive = ti < nt;
+          unsigned long long key = 0;
+          float4 box = make_float4(0.f, 0.f, 0.f, 0.f);
+          long long grp = 0;
+          if (alive) {
+            key = __ldcg(keys + base + ti);
+            box = __ldcg(bbox + base + ti);
+            grp = __ldcg(bgrp + base + ti);
+            const float area = box_area(box);
+            if (csz > 1) {
+              unsigned dw;
+              asm volatile("ld.relaxed.gpu.u32 %0, [%1];" : "=r"(dw) : "l"(dead + (p & 1) * kTileWords + (ti >> 5)) : "memory");
+              alive = !((dw >> (ti & 31)) & 1u);
+              // boxes kept by tile p-1 (the testers of phase p-1 could not know them)
+              for (int q = half; alive && q < npk; q += 2)
+                if (p_grp[q] == grp && suppresses(p_box[q], box_area(p_box[q]), box, area, iou_thr))
+                  alive = false;
+            } else {
+              // a group of one CTA: the whole kept list, unpipelined
+              for (int q = half; alive && q < nkept; q += 2) {
+                const float4 kb = __ldcg(kept_box + q);
+                if (__ldcg(kept_grp + q) == grp && suppresses(kb, box_area(kb), box, area, iou_thr))
+                  alive = false;
+              }
+            }
+          }
+          if (half == 0) {
+            t_box[ti] = box;
+            t_grp[ti] = grp;
+          }
+          {
+            const unsigned am = __ballot_sync(0xffffffffu, alive);
+            if (lane == 0) s_al[half][wid & (kTileWords - 1)] = am;
+          }
+          __syncthreads();
+          if (csz > 1 && threadIdx.x < kTileWords) dead[(p & 1) * kTileWords + threadIdx.x] = 0u;
+          // suppression bits among the survivors (upper triangle)
+          for (int item = wid; item < nt * nwords; item += kBigThreads / 32) {
+            const int rr = item / nwords, w = item - rr * nwords;
+            if (w < (rr >> 5)) continue;
+            const unsigned al_r = s_al[0][rr >> 5] & s_al[1][rr >> 5];
+            if (!((al_r >> (rr & 31)) & 1u)) continue;
+            const int j = w * 32 + lane;
+            const unsigned al_w = s_al[0][w] & s_al[1][w];
+            bool hit = false;
+            if (j > rr && ((al_w >> lane) & 1u)) {
+              const float4 br = t_box[rr], bj = t_box[j];
+              hit = t_grp[rr] == t_grp[j] && suppresses(br, box_area(br), bj, box_area(bj), iou_thr);
+            }
+            const unsigned m = __ballot_sync(0xffffffffu, hit);
+            if (lane == 0) mask[rr * kTileWords + w] = m;
+          }
+          __syncthreads();
+          if (wid == 0) {
+            unsigned rem = (lane < nwords) ? ~(s_al[0][lane] & s_al[1][lane]) : ~0u;
+            unsigned keep = 0u;
+            for (int w = 0; w < nwords; ++w) {
+              unsigned cur = __shfl_sync(0xffffffffu, rem, w);
+              unsigned kw = 0u;
+              while (~cur) {
+                const int j = __ffs(~cur) - 1;
+                kw |= 1u << j;
+                const int rr = w * 32 + j;
+                const unsigned mrow = (lane >= w && lane < nwords) ? mask[rr * kTileWords + lane] : 0u;
+                rem |= mrow;
+                cur |= __shfl_sync(0xffffffffu, mrow, w) | ((2u << j) - 1u);
+              }
+              if (lane == w) keep = kw;
+            }
+            s_keep[lane] = keep;
+          }
+          __syncthreads();
+          int before_k = 0, total_k = 0;
+#pragma unroll
+          for (int w = 0; w < kTileWords; ++w) {
+            const int c = __popc(s_keep[w]);
+            if (w < (ti >> 5)) before_k += c;
+            total_k += c;
+          }
+          const unsigned kwm = s_keep[ti >> 5];
+          if (half == 0 && ((kwm >> (ti & 31)) & 1u)) {
+            const int lp = before_k + __popc(kwm & ((1u << (ti & 31)) - 1u));
+            kept_key[nkept + lp] = key;
+            kept_box[nkept + lp] = box;
+            kept_grp[nkept + lp] = grp;
+            p_box[lp] = box;
+            p_grp[lp] = grp;
+          }
+          nkept += total_k;
+          npk = total_k;
+          // what the testers of phase p+1 work against: everything kept by tiles <= p
+          if (threadIdx.x == 0) nk_pub[(p + 1) & 1] = nkept;
+        } else if (p + 1 < ntiles) {
+          // tester: tile p+1 against the boxes kept by tiles < p
+          int n0;
+          asm volatile("ld.relaxed.gpu.s32 %0, [%1];" : "=r"(n0) : "l"(nk_pub + (p & 1)) : "memory");
+          const int T = csz - 1, tr = r - 1;
+          const int lo = (int)((long long)n0 * tr / T), hi = (int)((long long)n0 * (tr + 1) / T);
+          const int base = (p + 1) * kTile;
+          const int nt = min(K - base, kTile);
+          bool hit = false;
+          float4 box = make_float4(0.f, 0.f, 0.f, 0.f);
+          long long grp = 0;
+          if (ti < nt && lo < hi) {
+            box = __ldcg(bbox + base + ti);
+            grp = __ldcg(bgrp + base + ti);
+          }
+          const float area = box_area(box);
+          // my share of the kept list goes through shared memory (L2 -> smem once per CTA, then
+          // broadcast reads); __ldcg: other CTAs wrote these lines during this kernel
+          float4* st_box = reinterpret_cast<float4*>(s_keys);                 // kStage x 16 B
+          long long* st_grp = reinterpret_cast<long long*>(st_box + kStage);  // kStage x 8 B
+          for (int c0 = lo; c0 < hi; c0 += kStage) {
+            const int cnt = min(kStage, hi - c0);
+            for (int i = threadIdx.x; i < cnt; i += kBigThreads) {
+              st_box[i] = __ldcg(kept_box + c0 + i);
+              st_grp[i] = __ldcg(kept_grp + c0 + i);
+            }
+            __syncthreads();
+            if (ti < nt && !hit) {
+              for (int q = half; q < cnt; q += 2) {
+                const float4 kb = st_box[q];
+                if (st_grp[q] == grp && suppresses(kb, box_area(kb), box, area, iou_thr)) {
+                  hit = true;
+                  break;
+                }
+              }
+            }
+            __syncthreads();
+          }
+          const unsigned m = __ballot_sync(0xffffffffu, hit);
+          if (lane == 0 && m) atomicOr(dead + ((p + 1) & 1) * kTileWords + (wid & (kTileWords - 1)), m);
+        }
+        if (csz > 1) group_sync(ctr, target, csz);
+        else __syncthreads();
+      }
+      if (r == 0 && threadIdx.x == 0) v.kept_count[seg] = nkept;
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------------
 // ordered compaction of the kept lists
 // ---------------------------------------------------------------------------------
@@ -461,6 +827,9 @@ nms_emit_kernel(const SegView v, const int S, const int N, long long* __restrict
   __syncthreads();
   const int mine = v.kept_count[seg];
   if (threadIdx.x == 0) {
+    // both greedy kernels have read the candidate count: leave it 0 for the next filter pass
+    // (a per-call memset node would sit behind the dense store stream in the overlapped step)
+    v.count[seg] = 0;
     int tot = 0;
     for (int i = 0; i < 8; ++i) tot += s_warp[i];
     s_base = tot;
@@ -698,17 +1067,59 @@ static int next_pow2(long long x) {
   return (int)p;
 }
 
+// cudaFuncSetAttribute is per device: one flag per (kernel instantiation, device).  The
+// reference calls this path from one OS thread per device inside one process
+// (train/src/train/multi_gpu.rs:578-646); a race between threads only repeats the call.
+constexpr int kMaxDevices = 64;
+
 template <class P>
-static int launch_segments(const P& prov, const SegView& v, int S, double iou_thr, cudaStream_t s) {
-  static bool attr_set = false;  // idempotent; a race only repeats the call
+static int launch_segments(YhWorkspace* ws, const P& prov, SegView v, int S, double iou_thr,
+                           cudaStream_t s) {
+  static bool seg_attr[kMaxDevices] = {};
+  static bool big_attr[kMaxDevices] = {};
+  const int dev = ws->device;
   const size_t smem = kSegSmem;
-  if (!attr_set) {
+  if (dev >= kMaxDevices || !seg_attr[dev]) {
     YH_CUDA(cudaFuncSetAttribute(nms_segment_kernel<P>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)smem));
-    attr_set = true;
+    if (dev < kMaxDevices) seg_attr[dev] = true;
   }
+  // segments above kBigMin candidates need the big buffers; a workspace without them (candidate
+  // capacity <= kBigMin) cannot hold such a segment in the first place
+  const bool big = ws->big_box != nullptr && v.cap > kBigMin;
+  v.big_min = big ? kBigMin : 0;
   YH_TIME(YH_K_NMS_SEGMENT, s);
   nms_segment_kernel<P><<<S, kNmsThreads, smem, s>>>(prov, v, iou_thr);
+  YH_LAUNCHED(s);
+  if (!big) return YH_OK;
+  // the multi-CTA kernel: one CTA per SM, co-resident (cooperative launch: its groups spin on
+  // their own barriers); exits at once when no segment is big
+  const size_t big_smem = (size_t)kSortTile * sizeof(unsigned long long);
+  if (dev >= kMaxDevices || !big_attr[dev]) {
+    YH_CUDA(cudaFuncSetAttribute(nms_big_kernel<P>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)big_smem));
+    if (dev < kMaxDevices) big_attr[dev] = true;
+  }
+  BigView bv;
+  bv.box = ws->big_box;
+  bv.grp = ws->big_grp;
+  bv.len = ws->big_len;
+  bv.sync = ws->big_sync;
+  bv.dead = ws->big_sync + kBigGroups * 32;
+  bv.nkept = (int*)(ws->big_sync + kBigGroups * 32 + kBigGroups * 2 * kTileWords);
+  YH_CUDA(cudaMemsetAsync(ws->big_sync, 0, YH_BIG_SYNC_WORDS * sizeof(unsigned), s));
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)ws->num_sms);
+  cfg.blockDim = dim3(kBigThreads);
+  cfg.dynamicSmemBytes = big_smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeCooperative;
+  attr[0].val.cooperative = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  YH_TIME(YH_K_NMS_BIG, s);
+  YH_CUDA(cudaLaunchKernelEx(&cfg, nms_big_kernel<P>, prov, v, S, bv, iou_thr));
   YH_LAUNCHED(s);
   return YH_OK;
 }
@@ -724,6 +1135,8 @@ static SegView make_view(YhWorkspace* ws) {
   v.stride = ws->cand_stride;
   v.cap = ws->cand_per_image;
   v.seg_off = nullptr;
+  v.need = ws->cand_need;
+  v.big_min = 0;
   return v;
 }
 
@@ -776,7 +1189,7 @@ int yh_nms(YhWorkspace* ws, const float* const* heads, const YhLayer* layers, in
   else YH_FILTER(1);
 #undef YH_FILTER
   YH_LAUNCHED(s);
-  rc = launch_segments(prov, v, B, iou_threshold, s);
+  rc = launch_segments(ws, prov, v, B, iou_threshold, s);
   if (rc) return rc;
   YH_TIME(YH_K_NMS_EMIT, s);
   nms_emit_kernel<<<B, 256, 0, s>>>(v, B, prov.t.N, (long long*)kb, (long long*)kc,
@@ -836,7 +1249,7 @@ int yh_nms_by_scores(YhWorkspace* ws, const float* ltrb, const float* scores,
     by_fill_kernel<<<blocks, 256, 0, s>>>(scores, (const long long*)groups, K, v.keys, by_off,
                                           by_cursor);
     YH_LAUNCHED(s);
-    int rc = launch_segments(prov, v, kBySegs, iou_threshold, s);
+    int rc = launch_segments(ws, prov, v, kBySegs, iou_threshold, s);
     if (rc) return rc;
     YH_TIME(YH_K_NMS_EMIT, s);
     by_rank_kernel<<<(K + kRankThreads / 32 - 1) / (kRankThreads / 32), kRankThreads, 0, s>>>(
@@ -849,7 +1262,7 @@ int yh_nms_by_scores(YhWorkspace* ws, const float* ltrb, const float* scores,
   YH_TIME(YH_K_NMS_PACK, s);
   nms_pack_kernel<<<(K + 255) / 256, 256, 0, s>>>(scores, K, v.keys, v.count);
   YH_LAUNCHED(s);
-  int rc = launch_segments(prov, v, 1, iou_threshold, s);
+  int rc = launch_segments(ws, prov, v, 1, iou_threshold, s);
   if (rc) return rc;
   YH_TIME(YH_K_NMS_EMIT, s);
   nms_emit_kernel<<<1, 256, 0, s>>>(v, 1, 1, nullptr, nullptr, nullptr, nullptr, nullptr,

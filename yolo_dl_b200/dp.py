@@ -63,6 +63,7 @@ class GradientAllReduce:
             cur_bytes += nbytes
         if cur:
             plan.append(cur)
+        self._views: List[torch.Tensor] = []   # per parameter, its slice of a bucket
         for ps in plan:
             flat = torch.zeros(sum(p.numel() for p in ps), dtype=ps[0].dtype, device=ps[0].device)
             o = 0
@@ -71,18 +72,40 @@ class GradientAllReduce:
                 if p.grad is not None:
                     v.copy_(p.grad)
                 p.grad = v
+                self._views.append(v)
                 o += p.numel()
             self.buckets.append(flat)
 
     def zero_grad(self) -> None:
+        """Zeroes the buckets and keeps `.grad` pointing into them.  Use this instead of
+        `optimizer.zero_grad()` / `model.zero_grad()`, whose default `set_to_none=True` drops the
+        views (reduce() then repairs the aliasing, at the price of one copy per parameter)."""
         for b in self.buckets:
             b.zero_()
+        self._reattach(copy=False)
+
+    def _reattach(self, copy: bool) -> None:
+        """Every `.grad` must alias its bucket slice, or the all-reduce averages stale buckets
+        while autograd accumulates elsewhere (after zero_grad(set_to_none=True) the next
+        backward allocates fresh .grad tensors).  A detached gradient is copied into its slice
+        and re-pointed; a missing one (parameter unused this step) counts as zero."""
+        for p, v in zip(self.params, self._views):
+            g = p.grad
+            if g is not None and g.data_ptr() == v.data_ptr() and g.shape == v.shape:
+                continue
+            if copy:
+                if g is None:
+                    v.zero_()
+                else:
+                    v.copy_(g)
+            p.grad = v
 
     def reduce(self, local_batch: int, global_batch: int, exact_order: bool = False, async_op: bool = False):
         """In place on the buckets.  Returns the list of work handles when `async_op`."""
         world = _world(self.group)
         handles = []
         with torch.no_grad():
+            self._reattach(copy=True)
             for b in self.buckets:
                 if exact_order:
                     b.mul_(float(local_batch))

@@ -220,6 +220,8 @@ class YoloLoss:
         iou_score = torch.empty(a.cap, dtype=torch.float32, device=dev)
         pred_rows = torch.empty((a.cap, C + 5), dtype=torch.float32, device=dev)
         grads = [torch.empty_like(h) for h in prediction.heads] if want_grad else None
+        if want_grad:
+            self._ws.reserve_rows(a.cap, C)
         with torch.cuda.device(dev):
             _lib.check(self._lib.yh_loss_fwd_bwd(
                 self._ws.handle, _lib.ptr_array(prediction.heads),

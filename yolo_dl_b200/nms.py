@@ -20,8 +20,13 @@ class NonMaxSuppressionInit:
     iou_threshold: float = 0.6
     confidence_threshold: float = 0.1
     suppress_by_class: bool = False
-    max_candidates_per_image: int = 8192   # capacity of the per-image candidate list
+    # Initial capacity of the per-image candidate list.  The reference takes whatever `nonzero()`
+    # returns (nms.rs:97-103); here a batch that outgrows the list is detected at the count read
+    # forward() does anyway, the workspace is re-created with the size the filter counted and the
+    # call repeated (`grow`), so the capacity is a starting point, not a limit.
+    max_candidates_per_image: int = 8192
     max_detections: int = 0                # output capacity; 0 = batch * max_candidates_per_image
+    grow: bool = True                      # False: an overflow raises YoloHotError(YH_ERR_CAPACITY)
 
     def build(self) -> "NonMaxSuppression":
         # nms.rs:35-39
@@ -56,6 +61,7 @@ class NonMaxSuppression:
         self.suppress_by_class = bool(init.suppress_by_class)
         self.max_candidates_per_image = int(init.max_candidates_per_image)
         self.max_detections = int(init.max_detections)
+        self.grow = bool(init.grow)
         self._lib = _lib.load()
         self._ws = Workspace()
 
@@ -80,11 +86,29 @@ class NonMaxSuppression:
                     out.tlbr.data_ptr(), out.conf.data_ptr(), out.K.data_ptr(), cap, s))
         return out
 
+    def _run(self, prediction: MergedDenseDetection, pick_best_class: bool):
+        """forward_raw + the synchronising count read; on a candidate-list overflow the workspace
+        grows to what the filter counted and the call is repeated (count -> allocate -> fill)."""
+        while True:
+            raw = self.forward_raw(prediction, pick_best_class)
+            try:
+                _, K = self._ws.read_counts(_stream(prediction.boxes), K_dev=raw.K)
+                return raw, K
+            except _lib.YoloHotError as e:
+                need = int(self._lib.yh_workspace_candidates_needed(self._ws.handle))
+                if not (self.grow and e.status == _lib.YH_ERR_CAPACITY and
+                        need > self.max_candidates_per_image):
+                    raise
+                del raw
+                cap = 1
+                while cap < need:
+                    cap <<= 1
+                self.max_candidates_per_image = cap
+
     def forward(self, prediction: MergedDenseDetection) -> NmsOutput:
         """nms.rs:72-170. Kept rows ordered by (batch, confidence desc, class*N+instance)."""
         with torch.no_grad():
-            raw = self.forward_raw(prediction)
-            _, K = self._ws.read_counts(_stream(prediction.boxes), K_dev=raw.K)
+            raw, K = self._run(prediction, False)
             return raw.output(K)
 
 
@@ -111,8 +135,7 @@ class YoloInference:
         """inference.rs:37-93: NMS, then per (batch, instance) the max-confidence class, on the
         device (the reference round-trips through the host)."""
         with torch.no_grad():
-            raw = self.nms.forward_raw(prediction, pick_best_class=True)
-            _, K = self.nms._ws.read_counts(_stream(prediction.boxes), K_dev=raw.K)
+            raw, K = self.nms._run(prediction, True)
             return raw.output(K)
 
 

@@ -21,7 +21,7 @@ from .workspace import Workspace
 
 class DeviceStep:
     def __init__(self, spec, batch: int, device: torch.device, loss: YoloLossInit = None,
-                 nms_conf=0.4, nms_iou=0.5, by_class=True, max_gt=None, cand_per_image=8192,
+                 nms_conf=0.4, nms_iou=0.5, by_class=True, max_gt=None, cand_per_image=4096,
                  max_detections=None, with_grad=True):
         self.lib = _lib.load()
         self.spec, self.B, self.dev = spec, batch, device
@@ -62,7 +62,7 @@ class DeviceStep:
         self.K = torch.zeros(1, dtype=i32, device=device)
         self._grad_ptrs = _lib.ptr_array(self.grads) if with_grad else None
         # staging of the matched-row gradients: reserved now, graphs cannot allocate
-        _lib.check(self.lib.yh_workspace_reserve_rows(self.ws.handle, self.mcap, self.C))
+        self.ws.reserve_rows(self.mcap, self.C)
         self._side = None
         self._pub_stream = None
         self._graph = None

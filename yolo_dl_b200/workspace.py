@@ -14,6 +14,7 @@ class Workspace:
         self._lib = _lib.load()
         self.handle = None
         self.key = None
+        self._rows = 0
 
     def ensure(self, device: torch.device, batch: int, instances: int, cand_per_image: int = 1):
         if not (isinstance(device, torch.device) and device.type == "cuda"):
@@ -29,7 +30,20 @@ class Workspace:
         _lib.check(self._lib.yh_workspace_create(idx, batch, instances, cand_per_image, ctypes.byref(h)))
         self.handle = h
         self.key = (idx, batch, instances, cand_per_image)
+        self._rows = 0
         return h
+
+    def reserve_rows(self, capacity: int, num_classes: int):
+        """yh_workspace_reserve_rows: staging of the matched-row gradients for `capacity` rows.
+        The loss entry points never allocate (they fail with YH_ERR_CAPACITY instead); this is the
+        caller-side reserve, grown geometrically so that a training loop reallocates (and
+        synchronises) only a handful of times."""
+        need = capacity * (5 + num_classes)
+        if need <= self._rows:
+            return
+        cap = max(capacity, 2 * (self._rows // (5 + num_classes)))
+        _lib.check(self._lib.yh_workspace_reserve_rows(self.handle, cap, num_classes))
+        self._rows = cap * (5 + num_classes)
 
     def read_counts(self, stream, M_dev=None, K_dev=None):
         """The one synchronising read (yh_read_counts); raises on a buffer overflow."""
