@@ -181,3 +181,49 @@ def test_benchmark_ratios_follow_reference_expressions():
     assert r.obj_precision == 0.25 and r.class_accuracy == 0.25
     r = ratios_from_counts(1000, 0, 0, 0, 0)
     assert r.obj_recall == 1.0 and r.obj_precision == 1.0 and r.class_accuracy == 1.0
+
+
+def _c_struct_fields(header, name):
+    """field names of `typedef struct NAME { ... } NAME;` in declaration order"""
+    import re
+    body = re.search(r"typedef struct %s \{(.*?)\} %s;" % (name, name), header, re.S).group(1)
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    out = []
+    for decl in body.split(";"):
+        decl = decl.strip()
+        if not decl:
+            continue
+        names = decl.split(None, 1)[1]
+        out += [re.sub(r"\[.*?\]", "", n).strip() for n in names.split(",")]
+    return out
+
+
+def test_integration_md_rust_block_matches_header():
+    """INTEGRATION.md's Rust `#[repr(C)]` structs and `extern "C"` block are what a maintainer
+    copies: every struct must list the header's fields in order (a stale struct makes the library
+    read past it) and every function the header declares must be bound, with the same number of
+    arguments."""
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    header = open(os.path.join(root, "include", "yolohot.h")).read()
+    doc = open(os.path.join(root, "INTEGRATION.md")).read()
+    rust = doc[doc.index("```rust"):doc.index("pub fn check(rc: c_int)")]
+    for name in ("YhLayer", "YhLossCfg"):
+        body = re.search(r"pub struct %s \{(.*?)\n\}" % name, rust, re.S).group(1)
+        body = re.sub(r"//.*", "", body)
+        rust_fields = [m.lower() for m in re.findall(r"pub (\w+)\s*:", body)]
+        c_fields = [f.lower() for f in _c_struct_fields(header, name)]
+        assert rust_fields == c_fields, (name, rust_fields, c_fields)
+    hdr = re.sub(r"/\*.*?\*/", "", header, flags=re.S)
+    c_fns = {m.group(1): m.group(2) for m in
+             re.finditer(r"\b(yh_\w+)\s*\(([^;{]*?)\)\s*;", hdr, re.S)}
+    rs = re.sub(r"//.*", "", rust)
+    rust_fns = {m.group(1): m.group(2) for m in re.finditer(r"pub fn (yh_\w+)\s*\((.*?)\)", rs, re.S)}
+    assert set(c_fns) == set(_lib.SYMBOLS), set(c_fns) ^ set(_lib.SYMBOLS)
+    assert set(rust_fns) == set(c_fns), set(rust_fns) ^ set(c_fns)
+
+    def nargs(a):
+        a = a.strip()
+        return 0 if a in ("", "void") else a.count(",") + 1
+    for f in c_fns:
+        assert nargs(c_fns[f]) == nargs(rust_fns[f]) == len(_lib.SYMBOLS[f][1]), f
