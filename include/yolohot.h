@@ -206,6 +206,38 @@ int yh_loss_finish(YhWorkspace* ws, const YhLayer* layers, int L, int B, int C,
                    int capacity, const YhLossCfg* cfg, float* losses4_dev,
                    float* const* grad_heads, void* stream);
 
+/* The same loss in RANGES of images, for callers that order their streams around the 126 MB L2
+ * (yolo_dl_b200/pipeline.py; YoloLoss::forward itself is one sequence, loss_.rs:233-256).  The
+ * batch is cut into num_ranges <= 16 contiguous image ranges [b_lo, b_hi) (b_lo a multiple of 4:
+ * every head tensor must start an image range on a 16-byte boundary); for each range
+ *   yh_loss_dense_range   the dense objectness pass over those images (B stays the WHOLE batch:
+ *                         the losses are normalised by it), then
+ *   yh_loss_rows_range    ordered after it: the matched rows of those images, their gradients
+ *                         stored straight over the dense gradient while its lines are still in
+ *                         the L2 (no staging buffer, no scatter pass; grad_heads NULL = forward
+ *                         only).  image_row_offsets_dev = yh_assign_image_offsets(ws) of the
+ *                         workspace whose yh_assign produced the match list, or NULL (the kernel
+ *                         then binary-searches the batch column);
+ * and, after all ranges, yh_loss_finish_ranges reduces the partial sums into losses4_dev.
+ * Results equal yh_loss_fwd_bwd's: gradients bit for bit, the four scalars to f32 rounding of a
+ * differently associated f64 sum. */
+int yh_loss_dense_range(YhWorkspace* ws, const float* const* heads, const YhLayer* layers, int L,
+                        int B, int C, int b_lo, int b_hi, int range_index, int num_ranges,
+                        const YhLossCfg* cfg, float* const* grad_heads, void* stream);
+int yh_loss_rows_range(YhWorkspace* ws, const float* const* heads, const YhLayer* layers, int L,
+                       int B, int C, int b_lo, int b_hi, int range_index, int num_ranges,
+                       const int64_t* m_batch, const int64_t* m_flat, const float* m_target,
+                       const int64_t* m_class, const int32_t* M_dev, int capacity,
+                       const int32_t* image_row_offsets_dev, const YhLossCfg* cfg,
+                       float* iou_score_dev, float* pred_rows_dev, float* const* grad_heads,
+                       void* stream);
+int yh_loss_finish_ranges(YhWorkspace* ws, const YhLayer* layers, int L, int B, int C,
+                          int num_ranges, const int32_t* M_dev, int capacity, const YhLossCfg* cfg,
+                          float* losses4_dev, void* stream);
+/* Device pointer to the [B+1] int32 first-row-of-image offsets of the match list the last yh_assign
+ * on this workspace produced (valid once that call has run on the stream). */
+const int32_t* yh_assign_image_offsets(const YhWorkspace* ws);
+
 /* ---- a12+a13: NonMaxSuppression::forward (`yolo-dl/src/loss/nms.rs:72-170`) incl. the
  * grouped greedy NMS of tch_nms::nms_by_scores (call site nms.rs:142-148).
  * conf = sigmoid(obj)*sigmoid(cls); candidates: sigmoid(obj) >= thr && conf >= thr (f32

@@ -98,7 +98,7 @@ def test_step_graph_publishes_one_step_behind(dev):
     step = DeviceStep(spec, B, dev)
     ex = ydist.PeerLossExchange(dev, local_batch=B, slots=4)
     step.capture(heads, gt, off, publisher=ex)
-    assert step.kernels_in_graph == DeviceStep.KERNELS_PER_STEP + 1
+    assert step.kernels_in_graph == step.expected_kernels() + 1
     for _ in range(3):
         step.replay()
     torch.cuda.synchronize()

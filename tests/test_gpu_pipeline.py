@@ -61,7 +61,7 @@ def test_overlapped_and_graph_equal_sequential_and_oracle(dev, name, B):
     same(seq, snapshot(step))
 
     step.capture(heads, gt, off)
-    assert step.kernels_in_graph == DeviceStep.KERNELS_PER_STEP
+    assert step.kernels_in_graph == step.expected_kernels()
     for _ in range(3):
         for g in step.grads:
             g.fill_(float("nan"))
@@ -82,6 +82,72 @@ def test_overlapped_and_graph_equal_sequential_and_oracle(dev, name, B):
     ok = onms.nms_forward(om, 0.3, 0.5, True)
     assert np.array_equal(seq["ki"].cpu().numpy(), ok["instances"])
     assert np.array_equal(seq["kc"].cpu().numpy(), ok["classes"])
+
+
+@pytest.mark.parametrize("name,B,group", [("small", 12, 4), ("small", 8, 8), ("yolov4_608", 16, 8),
+                                          ("yolov4_tiny_416", 20, 8)])
+def test_grouped_schedule_equals_sequential(dev, name, B, group, monkeypatch):
+    """The loss in L2-sized image ranges (yh_loss_dense_range -> yh_loss_rows_range per range,
+    gradients of the matched rows stored straight over the dense gradient, then
+    yh_loss_finish_ranges): every output is bit-identical to the one-sequence form except the four
+    loss scalars, whose f64 partial sums are associated differently (equal to f32 rounding).
+    Covers a last range shorter than the others and the graph replay."""
+    monkeypatch.setenv("YH_GROUP", str(group))
+    spec = synth.small_spec() if name == "small" else getattr(synth, name)()
+    om_, cm_ = (-2.0, -1.0) if name == "small" else (-3.5, -2.5)
+    heads = [h.to(dev) for h in synth.make_heads(spec, B, synth.SEED0 + 6, obj_mean=om_, cls_mean=cm_)]
+    targets = synth.make_targets(spec, B, synth.SEED0 + 6, n_max=12, clustered=0.3)
+    targets[1] = []                      # an image without labels inside a range
+    gt_h, off_h = yh.pack_labels(targets)
+    gt, off = gt_h.to(dev), off_h.to(dev)
+    step = DeviceStep(spec, B, dev, nms_conf=0.3, nms_iou=0.5, by_class=False)
+    step.run(heads, gt, off)
+    seq = snapshot(step)
+
+    def check():
+        got = snapshot(step)
+        torch.testing.assert_close(got["losses"], seq["losses"], rtol=2e-7, atol=0)
+        got["losses"] = seq["losses"]
+        same(seq, got)
+
+    for g in step.grads:
+        g.fill_(float("nan"))
+    step.losses4.fill_(float("nan"))
+    step.run_grouped(heads, gt, off)
+    check()
+    step.schedule = "grouped"
+    step.capture(heads, gt, off)
+    assert step.kernels_in_graph == step.expected_kernels(True)
+    for _ in range(2):
+        for g in step.grads:
+            g.fill_(float("nan"))
+        step.losses4.fill_(float("nan"))
+        step.replay()
+        check()
+    # without the per-image offsets of yh_assign the rows kernel searches the batch column itself
+    R = (B + group - 1) // group
+    hp = yh._lib.ptr_array(heads)
+    s = torch.cuda.current_stream(dev).cuda_stream
+    for g in step.grads:
+        g.fill_(float("nan"))
+    for r in range(R):
+        lo, hi = r * group, min(B, (r + 1) * group)
+        yh._lib.check(step.lib.yh_loss_dense_range(step.ws.handle, hp, step.layers, step.L, B, step.C, lo, hi,
+                                                   r, R, step.cfg, step._grad_ptrs, s))
+        yh._lib.check(step.lib.yh_loss_rows_range(
+            step.ws.handle, hp, step.layers, step.L, B, step.C, lo, hi, r, R, step.m_batch.data_ptr(),
+            step.m_flat.data_ptr(), step.m_target.data_ptr(), step.m_class.data_ptr(), step.M.data_ptr(),
+            step.mcap, None, step.cfg, step.iou_score.data_ptr(), step.pred_rows.data_ptr(),
+            step._grad_ptrs, s))
+    yh._lib.check(step.lib.yh_loss_finish_ranges(step.ws.handle, step.layers, step.L, B, step.C, R,
+                                                 step.M.data_ptr(), step.mcap, step.cfg,
+                                                 step.losses4.data_ptr(), s))
+    check()
+    # an image range must start on a 16-byte boundary of every head tensor
+    if name == "small":
+        rc = step.lib.yh_loss_dense_range(step.ws.handle, hp, step.layers, step.L, B, step.C, 1, 4, 0, 2,
+                                          step.cfg, step._grad_ptrs, s)
+        assert rc == yh._lib.YH_ERR_INVALID and b"multiple of 4" in step.lib.yh_last_error()
 
 
 def test_graph_replay_follows_refilled_inputs(dev):

@@ -164,7 +164,8 @@ assign_emit_kernel(int N, int B, const int words, const double* __restrict__ gt,
                    const int* __restrict__ img_count, long long* __restrict__ out_batch,
                    long long* __restrict__ out_flat, int* __restrict__ out_gt,
                    float* __restrict__ out_target, long long* __restrict__ out_class,
-                   int* __restrict__ out_M, int capacity, int* __restrict__ err_flag) {
+                   int* __restrict__ out_M, int capacity, int* __restrict__ err_flag,
+                   int* __restrict__ img_off) {
   __shared__ int s_warp[kEmitThreads / 32];
   __shared__ int s_base;
   __shared__ int s_list[kEmitList];
@@ -181,8 +182,10 @@ assign_emit_kernel(int N, int B, const int words, const double* __restrict__ gt,
     int tot = 0;
     for (int i = 0; i < kEmitThreads / 32; ++i) tot += s_warp[i];
     s_base = tot;
+    img_off[b] = tot;  // first row of image b in the match list (yh_assign_image_offsets)
     if (b == B - 1) {
       const int M = tot + img_count[b];
+      img_off[B] = M;
       *out_M = M;
       if (M > capacity) atomicOr(err_flag, 1);
     }
@@ -312,7 +315,11 @@ extern "C" int yh_assign(YhWorkspace* ws, const double* gt_dev, const int32_t* g
       t.N, B, words, gt_dev, gt_offsets_dev, ws->slot_dist, ws->slot_gt, ws->slot_bits,
       ws->img_count, (long long*)out_batch,
       (long long*)out_flat, out_gt, out_target, (long long*)out_class, out_M_dev, capacity,
-      ws->err_flag);
+      ws->err_flag, ws->img_off);
   YH_LAUNCHED(s);
   return YH_OK;
+}
+
+extern "C" const int32_t* yh_assign_image_offsets(const YhWorkspace* ws) {
+  return ws ? ws->img_off : nullptr;
 }

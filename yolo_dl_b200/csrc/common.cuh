@@ -159,6 +159,7 @@ struct YhWorkspace {
   int* slot_gt;                   // [max_batch * max_instances] winning GT (local index)
   unsigned* slot_bits;            // [max_batch * ceil(max_instances/32)] occupancy bitmap
   int* img_count;                 // [max_batch] matches per image
+  int* img_off;                   // [max_batch + 1] first match row of every image (assign_emit)
   unsigned long long* pick_slot;  // [max_batch * max_instances] scratch of yh_inference_pick
 
   // loss (loss.cu)

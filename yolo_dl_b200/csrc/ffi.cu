@@ -189,6 +189,7 @@ int yh_workspace_destroy(YhWorkspace* ws) {
   cudaFree(ws->slot_gt);
   cudaFree(ws->slot_bits);
   cudaFree(ws->img_count);
+  cudaFree(ws->img_off);
   cudaFree(ws->pick_slot);
   cudaFree(ws->partials);
   cudaFree(ws->ticket);
@@ -261,6 +262,7 @@ int yh_workspace_create(int device, int max_batch, int64_t max_instances, int ca
   YH_ALLOC(ws->slot_gt, slots * sizeof(int));
   YH_ALLOC(ws->slot_bits, (size_t)max_batch * (size_t)((max_instances + 31) / 32) * sizeof(unsigned));
   YH_ALLOC(ws->img_count, (size_t)max_batch * sizeof(int));
+  YH_ALLOC(ws->img_off, ((size_t)max_batch + 1) * sizeof(int));
   YH_ALLOC(ws->pick_slot, slots * sizeof(unsigned long long));
   YH_ALLOC(ws->partials, (size_t)YH_PARTIALS_MAX * 4 * sizeof(double));
   YH_ALLOC(ws->ticket, 64);

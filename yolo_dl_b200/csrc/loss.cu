@@ -493,8 +493,32 @@ __device__ __forceinline__ float hausdorff_metric(const Box4 p, const Box4 q, co
 constexpr int kRowsPerWarp = 8;
 constexpr int kClsRegs = 3;
 
+// An image range [b_lo, b_hi) of a batch (yh_loss_*_range): which rows of the (batch, flat)-sorted
+// match list belong to it.  img_off (the per-image row offsets yh_assign leaves in its workspace)
+// answers with two loads; without it every CTA binary-searches the batch column.
+struct RowRange {
+  int b_lo, b_hi;      // b_hi < 0: all rows
+  const int* img_off;  // [B+1] or null
+  int part_off;        // first partial-sum slot of this launch
+};
+
+__device__ __forceinline__ int first_row_of_image(const long long* __restrict__ m_batch, const int M,
+                                                  const int b) {
+  int lo = 0, hi = M;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (__ldg(m_batch + mid) < (long long)b) lo = mid + 1; else hi = mid;
+  }
+  return lo;
+}
+
+// DIRECT (g.grad[0] != null): the gradients of a row are stored straight over the dense gradient
+// instead of being staged for loss_finish_kernel.  Meant for a launch that FOLLOWS the dense pass
+// of the same few images while their gradient lines are still in the 126 MB L2: the ~85 4-byte
+// stores of a row then land in resident lines (no read-modify-write through DRAM, no staging
+// buffer, no scatter kernel).
 __global__ void __launch_bounds__(kRowThreads)
-loss_rows_kernel(const LayerTab t, const LossParams p,
+loss_rows_kernel(const LayerTab t, const GradTab g, const LossParams p, const RowRange rr,
                  const long long* __restrict__ m_batch, const long long* __restrict__ m_flat,
                  const float* __restrict__ m_target, const long long* __restrict__ m_class,
                  const int* __restrict__ M_dev, const int capacity,
@@ -503,7 +527,21 @@ loss_rows_kernel(const LayerTab t, const LossParams p,
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int warps = kRowThreads / 32;
   const int M = min(*M_dev, capacity);
-  const bool want_grad = row_grad != nullptr;
+  const bool direct = g.grad[0] != nullptr;
+  const bool want_grad = row_grad != nullptr || direct;
+  int m_begin = 0, m_end = M;
+  if (rr.b_hi >= 0) {
+    if (rr.img_off != nullptr) {
+      m_begin = min(__ldg(rr.img_off + rr.b_lo), M);
+      m_end = min(__ldg(rr.img_off + rr.b_hi), M);
+    } else {
+      __shared__ int s_rng[2];
+      if (threadIdx.x < 2) s_rng[threadIdx.x] = first_row_of_image(m_batch, M, threadIdx.x ? rr.b_hi : rr.b_lo);
+      __syncthreads();
+      m_begin = s_rng[0];
+      m_end = s_rng[1];
+    }
+  }
   const bool haus = p.metric == YH_METRIC_HAUSDORFF;
   const float Mf = (float)M;
   const float MCf = (float)((long long)M * t.C);
@@ -511,11 +549,11 @@ loss_rows_kernel(const LayerTab t, const LossParams p,
 
   double a_iou = 0.0, a_cls = 0.0, a_obj = 0.0;
 
-  for (int m0 = (blockIdx.x * warps + wid) * kRowsPerWarp; m0 < M;
+  for (int m0 = m_begin + (blockIdx.x * warps + wid) * kRowsPerWarp; m0 < m_end;
        m0 += gridDim.x * warps * kRowsPerWarp) {
     // ---- phase A, part 1: where is my row -------------------------------------------
     const int m = m0 + lane;
-    const bool own = lane < kRowsPerWarp && m < M;
+    const bool own = lane < kRowsPerWarp && m < m_end;
     long long off = 0;     // offset of entry 0 of the row inside its head tensor
     int es = 0, l = 0, cls = 0, anchor = 0, row = 0, col = 0;
     float4 tg = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -549,7 +587,7 @@ loss_rows_kernel(const LayerTab t, const LossParams p,
 #pragma unroll
       for (int j = 0; j < kClsRegs; ++j) {
         const int k = lane + 32 * j;
-        xc[r][j] = (m0 + r < M && k < t.C) ? hp[(size_t)(5 + k) * es_r] : 0.0f;
+        xc[r][j] = (m0 + r < m_end && k < t.C) ? hp[(size_t)(5 + k) * es_r] : 0.0f;
       }
     }
 
@@ -593,16 +631,18 @@ loss_rows_kernel(const LayerTab t, const LossParams p,
         r[0] = pb.cy; r[1] = pb.cx; r[2] = pb.h; r[3] = pb.w; r[4] = xo;
       }
       if (want_grad) {
-        // staged per row ([M, 5+C], coalesced); loss_finish_kernel scatters it into the heads
-        float* gp = row_grad + (size_t)m * t.E;
+        // staged per row ([M, 5+C], coalesced); loss_finish_kernel scatters it into the heads —
+        // or, DIRECT, entry e of the row goes to its place in the dense gradient (stride es)
+        float* gp = direct ? g.grad[l] + off : row_grad + (size_t)m * t.E;
+        const size_t gs = direct ? (size_t)es : (size_t)1;
         // chain through the decode (detect_2d.rs:69-72,122-133):
         //   cy = (2s-0.5)/H + off  -> dcy/ds = 2/H ; s' = s(1-s)
         //   h  = (2s)^2 * a        -> dh/ds  = a * 2*(2s) * 2
         const float Hf = (float)t.H[l], Wf = (float)t.W[l];
         gp[0] = (d.cy / Hf * 2.0f) * ((1.0f - s0) * s0);
-        gp[1] = (d.cx / Wf * 2.0f) * ((1.0f - s1) * s1);
-        gp[2] = ((d.h * t.ah[l][anchor]) * (2.0f * (s2 * 2.0f)) * 2.0f) * ((1.0f - s2) * s2);
-        gp[3] = ((d.w * t.aw[l][anchor]) * (2.0f * (s3 * 2.0f)) * 2.0f) * ((1.0f - s3) * s3);
+        gp[gs] = (d.cx / Wf * 2.0f) * ((1.0f - s1) * s1);
+        gp[2 * gs] = ((d.h * t.ah[l][anchor]) * (2.0f * (s2 * 2.0f)) * 2.0f) * ((1.0f - s2) * s2);
+        gp[3 * gs] = ((d.w * t.aw[l][anchor]) * (2.0f * (s3 * 2.0f)) * 2.0f) * ((1.0f - s3) * s3);
         // objectness gradient with the real target (replaces K4's target-0 value)
         const float so = sigmoid_f(xo);
         float gi;
@@ -615,7 +655,7 @@ loss_rows_kernel(const LayerTab t, const LossParams p,
           gi = so - to;
         }
         if (p.reduction == YH_REDUCTION_MEAN) gi = gi / numel_obj;
-        gp[4] = gi * p.w_obj;
+        gp[4 * gs] = gi * p.w_obj;
       }
     }
 
@@ -626,9 +666,11 @@ loss_rows_kernel(const LayerTab t, const LossParams p,
       const int es_r = __shfl_sync(0xffffffffu, es, r);
       const int l_r = __shfl_sync(0xffffffffu, l, r);
       const int cls_r = __shfl_sync(0xffffffffu, cls, r);
-      if (m0 + r >= M) break;  // warp-uniform
+      if (m0 + r >= m_end) break;  // warp-uniform
       const float* hp = t.head[l_r] + off_r;
-      float* gp = want_grad ? row_grad + (size_t)(m0 + r) * t.E : nullptr;
+      float* gp = !want_grad ? nullptr
+                             : (direct ? g.grad[l_r] + off_r : row_grad + (size_t)(m0 + r) * t.E);
+      const size_t gs = direct ? (size_t)es_r : (size_t)1;
       float bce = 0.f;
       // CrossEntropyLoss (cross_entropy.rs:19-58): the dense target's arg-max (first maximum:
       // the class, or 0 when pos == neg), log_softmax + nll per ROW
@@ -675,7 +717,7 @@ loss_rows_kernel(const LayerTab t, const LossParams p,
           bce += kind_loss(p.cls_kind, x, tt, false, 0.0f, p.gamma, gi);
           if (p.reduction == YH_REDUCTION_MEAN) gi = gi / MCf;
         }
-        if (want_grad) gp[5 + k] = gi * p.w_cls;
+        if (want_grad) gp[(size_t)(5 + k) * gs] = gi * p.w_cls;
         if (pred_rows) pred_rows[(size_t)(m0 + r) * t.E + 5 + k] = x;
       }
       bce = warp_sum(bce);
@@ -701,7 +743,7 @@ loss_rows_kernel(const LayerTab t, const LossParams p,
       s[1] += s_acc[k][1];
       s[2] += s_acc[k][2];
     }
-    double* dst = partials + (size_t)(kPartHalf + blockIdx.x) * 4;
+    double* dst = partials + (size_t)(kPartHalf + rr.part_off + blockIdx.x) * 4;
     dst[0] = s[0];
     dst[1] = s[1];
     dst[2] = s[2];
@@ -722,8 +764,9 @@ loss_finish_kernel(const LayerTab t, const GradTab g, const LossParams p,
                    const long long* __restrict__ m_batch, const long long* __restrict__ m_flat,
                    const int* __restrict__ M_dev, const int capacity,
                    const float* __restrict__ row_grad, const double* __restrict__ partials,
-                   const int n_dense_partials, const int n_row_partials,
-                   float* __restrict__ losses4, int* __restrict__ err_flag) {
+                   const int dense_per_range, const int rows_per_range, const int num_ranges,
+                   const int range_stride, float* __restrict__ losses4,
+                   int* __restrict__ err_flag) {
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int warps = kFinishThreads / 32;
   const int M = min(*M_dev, capacity);
@@ -803,13 +846,17 @@ loss_finish_kernel(const LayerTab t, const GradTab g, const LossParams p,
   // every thread sums a strided subset; the loads of a thread are independent of its sums,
   // so they are issued kFinalUnroll at a time (the association is still a fixed one)
   constexpr int kFinalUnroll = 8;
+  // launch r of a ranged loss (yh_loss_*_range) wrote its partials from slot r * range_stride
+  const int n_dense_partials = dense_per_range * num_ranges;
+  const int n_row_partials = rows_per_range * num_ranges;
   double r[4] = {0.0, 0.0, 0.0, 0.0};
   for (int i0 = threadIdx.x; i0 < n_dense_partials; i0 += kFinishThreads * kFinalUnroll) {
     double v[kFinalUnroll];
 #pragma unroll
     for (int u = 0; u < kFinalUnroll; ++u) {
       const int i = i0 + u * kFinishThreads;
-      v[u] = (i < n_dense_partials) ? __ldcg(&partials[(size_t)i * 4]) : 0.0;
+      const int slot = (i / dense_per_range) * range_stride + i % dense_per_range;
+      v[u] = (i < n_dense_partials) ? __ldcg(&partials[(size_t)slot * 4]) : 0.0;
     }
 #pragma unroll
     for (int u = 0; u < kFinalUnroll; ++u) r[3] += v[u];
@@ -819,7 +866,8 @@ loss_finish_kernel(const LayerTab t, const GradTab g, const LossParams p,
 #pragma unroll
     for (int u = 0; u < kFinalUnroll; ++u) {
       const int i = i0 + u * kFinishThreads;
-      const double* src = partials + (size_t)(kPartHalf + i) * 4;
+      const int slot = (i / rows_per_range) * range_stride + i % rows_per_range;
+      const double* src = partials + (size_t)(kPartHalf + slot) * 4;
 #pragma unroll
       for (int k = 0; k < 3; ++k) v[u][k] = (i < n_row_partials) ? __ldcg(&src[k]) : 0.0;
     }
@@ -873,18 +921,31 @@ namespace yh {
 
 enum { kPhaseDense = 1, kPhaseRows = 2, kPhaseFinish = 4 };
 
+// One launch of a RANGED loss: images [b_lo, b_hi) of a batch of B, launch `index` of `count`.
+// count == 0: the plain whole-batch call.
+struct LossRange {
+  int b_lo, b_hi, index, count;
+  const int32_t* img_off;  // per-image row offsets of the match list ([B+1], device) or null
+  int direct;              // rows phase: scatter straight into grad_heads (no staging, no finish scatter)
+};
+constexpr int kMaxRanges = 16;
+constexpr int kRangeSlots = kPartHalf / kMaxRanges;  // partial-sum slots per ranged launch
+
 // The three phases of YoloLoss::forward+backward.
 //   kPhaseDense   needs only the heads;
 //   kPhaseRows    needs the heads and the matches (yh_assign); stages the row gradients in the
-//                 workspace, so it may run concurrently with kPhaseDense on another stream;
-//   kPhaseFinish  ordered after both: scatters the staged rows over the dense gradient and
-//                 reduces the partial sums into losses4.
+//                 workspace, so it may run concurrently with kPhaseDense on another stream — or,
+//                 ranged + direct, stores them over the dense gradient of the same images (then
+//                 it is ordered after that range's kPhaseDense);
+//   kPhaseFinish  ordered after both: scatters the staged rows over the dense gradient (not
+//                 after direct rows) and reduces the partial sums into losses4.
 static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
                        const YhLayer* layers, int L, int B, int C, const int64_t* m_batch,
                        const int64_t* m_flat, const float* m_target, const int64_t* m_class,
                        const int32_t* M_dev, int capacity, const YhLossCfg* cfg,
                        float* losses4_dev, float* iou_score_dev, float* pred_rows_dev,
-                       float* const* grad_heads, int want_grad_rows, void* stream) {
+                       float* const* grad_heads, int want_grad_rows, void* stream,
+                       const LossRange* range = nullptr) {
   YH_REQUIRE(ws != nullptr, "workspace is NULL");
   YH_REQUIRE(cfg != nullptr, "NULL argument");
   if (phases & kPhaseRows) {
@@ -894,10 +955,21 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
   }
   if (phases & kPhaseFinish) {
     YH_REQUIRE(losses4_dev != nullptr && M_dev != nullptr, "NULL argument");
-    YH_REQUIRE(capacity == 0 || (m_batch && m_flat), "match list is NULL");
+    YH_REQUIRE(capacity == 0 || grad_heads == nullptr || (m_batch && m_flat), "match list is NULL");
   }
   YH_REQUIRE(capacity >= 0, "capacity=%d", capacity);
   YH_REQUIRE(B >= 1 && B <= ws->max_batch, "B=%d outside 1..max_batch=%d", B, ws->max_batch);
+  const bool ranged = range != nullptr && range->count > 0;
+  const int num_ranges = ranged ? range->count : 1;
+  if (ranged) {
+    YH_REQUIRE(range->count <= kMaxRanges, "num_ranges=%d outside 1..%d", range->count, kMaxRanges);
+    if (!(phases & kPhaseFinish)) {
+      YH_REQUIRE(range->index >= 0 && range->index < range->count, "range_index=%d outside 0..%d",
+                 range->index, range->count - 1);
+      YH_REQUIRE(range->b_lo >= 0 && range->b_lo < range->b_hi && range->b_hi <= B,
+                 "image range [%d,%d) outside the batch of %d", range->b_lo, range->b_hi, B);
+    }
+  }
   LayerTab tab;
   int rc = build_layer_tab(layers, L, C, heads, &tab);
   if (rc) return rc;
@@ -960,47 +1032,66 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
     const int v = e ? atoi(e) : 0;
     return v > 0 ? v : 2;
   }();
+  const int slot_room = ranged ? kRangeSlots : kPartHalf;
   int dense_grid = ws->num_sms * dense_cps;
-  if (dense_grid > kPartHalf) dense_grid = kPartHalf;
-  // with a gradient: dense_grid objectness CTAs followed by one CTA per 32 KB tile
-  DenseTab dt;
-  memset(&dt, 0, sizeof(dt));
-  dt.L = L;
-  for (int l = 0; l < YH_MAX_LAYERS; ++l) {
-    long long tiles = 0, oq = 0;
-    if (l < L) {
-      dt.run[l] = (long long)tab.A[l] * tab.HW[l];
-      const long long quads = ((long long)B * dt.run[l] * tab.E + 3) / 4;
-      tiles = (quads + kTileQuads - 1) / kTileQuads;
-      oq = (long long)B * (dt.run[l] / 4 + 2);
-    }
-    dt.tile_prefix[l + 1] = dt.tile_prefix[l] + tiles;
-    dt.qprefix[l + 1] = dt.qprefix[l] + oq;
-  }
-  const long long dense_tiles = dt.tile_prefix[YH_MAX_LAYERS];
-  YH_REQUIRE(dense_tiles + dense_grid < (1LL << 31), "head tensors too large for one launch");
+  if (dense_grid > slot_room) dense_grid = slot_room;
+  int row_grid = ws->num_sms * 4;  // resident in one wave; rows beyond that grid-stride
+  const int rows_per_cta = (kRowThreads / 32) * kRowsPerWarp;
+  const int need = (capacity + rows_per_cta - 1) / rows_per_cta;
+  if (row_grid > need) row_grid = need;
+  if (row_grid < 1) row_grid = 1;
+  if (row_grid > slot_room) row_grid = slot_room;
+  const int part_off = ranged ? range->index * kRangeSlots : 0;
+
   if (phases & kPhaseDense) {
+    // the images of this launch: the whole batch, or [b_lo, b_hi) of it — the same kernel on
+    // pointers advanced by b_lo images (the loss is normalised by the WHOLE batch: numel)
+    const int b_lo = ranged ? range->b_lo : 0;
+    const int Bd = ranged ? range->b_hi - range->b_lo : B;
+    LayerTab dt_tab = tab;
+    GradTab dg = g;
+    DenseTab dt;
+    memset(&dt, 0, sizeof(dt));
+    dt.L = L;
+    for (int l = 0; l < YH_MAX_LAYERS; ++l) {
+      long long tiles = 0, oq = 0;
+      if (l < L) {
+        dt.run[l] = (long long)tab.A[l] * tab.HW[l];
+        const long long shift = (long long)b_lo * dt.run[l] * tab.E;  // floats
+        YH_REQUIRE(shift % 4 == 0,
+                   "b_lo=%d: layer %d has %lld floats per image, an image range must start at a "
+                   "16-byte boundary of every head tensor (use a multiple of 4 images)",
+                   b_lo, l, dt.run[l] * tab.E);
+        dt_tab.head[l] = tab.head[l] + shift;
+        if (grad_heads) dg.grad[l] = g.grad[l] + shift;
+        const long long quads = ((long long)Bd * dt.run[l] * tab.E + 3) / 4;
+        tiles = (quads + kTileQuads - 1) / kTileQuads;
+        oq = (long long)Bd * (dt.run[l] / 4 + 2);
+      }
+      dt.tile_prefix[l + 1] = dt.tile_prefix[l] + tiles;
+      dt.qprefix[l + 1] = dt.qprefix[l] + oq;
+    }
+    // with a gradient: dense_grid objectness CTAs followed by one CTA per 32 KB tile
+    const long long dense_tiles = dt.tile_prefix[YH_MAX_LAYERS];
+    YH_REQUIRE(dense_tiles + dense_grid < (1LL << 31), "head tensors too large for one launch");
     const bool bce = p.obj_kind == YH_LOSS_BCE;
+    double* part = ws->partials + (size_t)part_off * 4;
     YH_TIME(YH_K_LOSS_DENSE, s);
 #define YH_DENSE(G, K)                                                                       \
   loss_dense_kernel<G, K><<<(unsigned)(dense_grid + (G ? dense_tiles : 0)), kDenseThreads, 0, s>>>( \
-      tab, g, B, numel, p.w_obj, p.reduction, p.obj_kind, p.gamma, ws->partials, dense_grid, dt)
+      dt_tab, dg, Bd, numel, p.w_obj, p.reduction, p.obj_kind, p.gamma, part, dense_grid, dt)
     if (grad_heads) {
       if (bce) YH_DENSE(true, true); else YH_DENSE(true, false);
     } else {
       if (bce) YH_DENSE(false, true); else YH_DENSE(false, false);
     }
 #undef YH_DENSE
+    YH_LAUNCHED(s);
   }
-  if (phases & kPhaseDense) YH_LAUNCHED(s);
-  int row_grid = ws->num_sms * 4;  // resident in one wave; rows beyond that grid-stride
-  const int rows_per_cta = (kRowThreads / 32) * kRowsPerWarp;
-  const int need = (capacity + rows_per_cta - 1) / rows_per_cta;
-  if (row_grid > need) row_grid = need;
-  if (row_grid < 1) row_grid = 1;
-  if (row_grid > kPartHalf) row_grid = kPartHalf;
+  const bool direct = ranged && range->direct && grad_heads != nullptr;
   const bool want_grad = grad_heads != nullptr || want_grad_rows != 0;
-  if (want_grad && (phases & (kPhaseRows | kPhaseFinish)) && capacity > 0 &&
+  const bool staged = want_grad && !direct && !(ranged && (phases & kPhaseFinish) && !grad_heads);
+  if (staged && (phases & (kPhaseRows | kPhaseFinish)) && capacity > 0 &&
       (size_t)capacity * (size_t)tab.E > ws->row_grad_floats) {
     // no allocation and no synchronisation inside a compute entry point (yolohot.h conventions)
     set_error("row-gradient staging holds %zu floats, capacity=%d rows of %d need %zu: call "
@@ -1009,11 +1100,19 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
     return YH_ERR_CAPACITY;
   }
   if (phases & kPhaseRows) {
+    RowRange rr;
+    rr.b_lo = ranged ? range->b_lo : 0;
+    rr.b_hi = ranged ? range->b_hi : -1;
+    rr.img_off = ranged ? range->img_off : nullptr;
+    rr.part_off = part_off;
+    GradTab rg;
+    memset(&rg, 0, sizeof(rg));
+    if (direct) rg = g;
     YH_TIME(YH_K_LOSS_ROWS, s);
     loss_rows_kernel<<<row_grid, kRowThreads, 0, s>>>(
-        tab, p, (const long long*)m_batch, (const long long*)m_flat, m_target,
+        tab, rg, p, rr, (const long long*)m_batch, (const long long*)m_flat, m_target,
         (const long long*)m_class, M_dev, capacity, iou_score_dev, pred_rows_dev,
-        want_grad ? ws->row_grad : nullptr, ws->partials);
+        (want_grad && !direct) ? ws->row_grad : nullptr, ws->partials);
     YH_LAUNCHED(s);
   }
   if (phases & kPhaseFinish) {
@@ -1025,8 +1124,8 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
     YH_TIME(YH_K_LOSS_FINISH, s);
     loss_finish_kernel<<<fin_grid, kFinishThreads, 0, s>>>(
         tab, g, p, (const long long*)m_batch, (const long long*)m_flat, M_dev, capacity,
-        grad_heads ? ws->row_grad : nullptr, ws->partials, dense_grid, row_grid, losses4_dev,
-        ws->err_flag);
+        grad_heads ? ws->row_grad : nullptr, ws->partials, dense_grid, row_grid, num_ranges,
+        kRangeSlots, losses4_dev, ws->err_flag);
     YH_LAUNCHED(s);
   }
   return YH_OK;
@@ -1084,6 +1183,43 @@ int yh_loss_finish(YhWorkspace* ws, const YhLayer* layers, int L, int B, int C,
   return yh::loss_phases(yh::kPhaseFinish, ws, nullptr, layers, L, B, C, m_batch, m_flat, nullptr,
                          nullptr, M_dev, capacity, cfg, losses4_dev, nullptr, nullptr, grad_heads,
                          0, stream);
+}
+
+// ---- ranged forms: the batch in groups of images small enough for the L2 --------------------
+int yh_loss_dense_range(YhWorkspace* ws, const float* const* heads, const YhLayer* layers, int L,
+                        int B, int C, int b_lo, int b_hi, int range_index, int num_ranges,
+                        const YhLossCfg* cfg, float* const* grad_heads, void* stream) {
+  YH_REQUIRE(heads != nullptr, "heads is NULL");
+  yh::LossRange r = {b_lo, b_hi, range_index, num_ranges, nullptr, 0};
+  YH_REQUIRE(num_ranges >= 1, "num_ranges=%d", num_ranges);
+  return yh::loss_phases(yh::kPhaseDense, ws, heads, layers, L, B, C, nullptr, nullptr, nullptr,
+                         nullptr, nullptr, 0, cfg, nullptr, nullptr, nullptr, grad_heads, 0, stream,
+                         &r);
+}
+
+int yh_loss_rows_range(YhWorkspace* ws, const float* const* heads, const YhLayer* layers, int L,
+                       int B, int C, int b_lo, int b_hi, int range_index, int num_ranges,
+                       const int64_t* m_batch, const int64_t* m_flat, const float* m_target,
+                       const int64_t* m_class, const int32_t* M_dev, int capacity,
+                       const int32_t* image_row_offsets_dev, const YhLossCfg* cfg,
+                       float* iou_score_dev, float* pred_rows_dev, float* const* grad_heads,
+                       void* stream) {
+  YH_REQUIRE(heads != nullptr, "heads is NULL");
+  YH_REQUIRE(num_ranges >= 1, "num_ranges=%d", num_ranges);
+  yh::LossRange r = {b_lo, b_hi, range_index, num_ranges, image_row_offsets_dev, 1};
+  return yh::loss_phases(yh::kPhaseRows, ws, heads, layers, L, B, C, m_batch, m_flat, m_target,
+                         m_class, M_dev, capacity, cfg, nullptr, iou_score_dev, pred_rows_dev,
+                         grad_heads, 0, stream, &r);
+}
+
+int yh_loss_finish_ranges(YhWorkspace* ws, const YhLayer* layers, int L, int B, int C,
+                          int num_ranges, const int32_t* M_dev, int capacity, const YhLossCfg* cfg,
+                          float* losses4_dev, void* stream) {
+  YH_REQUIRE(num_ranges >= 1, "num_ranges=%d", num_ranges);
+  yh::LossRange r = {0, B, 0, num_ranges, nullptr, 1};
+  return yh::loss_phases(yh::kPhaseFinish, ws, nullptr, layers, L, B, C, nullptr, nullptr, nullptr,
+                         nullptr, M_dev, capacity, cfg, losses4_dev, nullptr, nullptr, nullptr, 0,
+                         stream, &r);
 }
 
 }  // extern "C"

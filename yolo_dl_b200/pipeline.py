@@ -66,6 +66,9 @@ class DeviceStep:
         self._side = None
         self._pub_stream = None
         self._graph = None
+        # "grouped": the loss in L2-sized image ranges (run_grouped); "overlapped": round 1's
+        # fork/join of whole-batch kernels (run_overlapped)
+        self.schedule = os.environ.get("YH_SCHEDULE", "grouped")
         self.kernels_in_graph = 0
 
     def algorithmic_bytes(self):
@@ -73,7 +76,22 @@ class DeviceStep:
         n = self.N * self.B
         return {"decode_kernel": 32 * n, "loss_dense_kernel": 344 * n, "nms_filter_kernel": 340 * n}
 
-    KERNELS_PER_STEP = 9
+
+    def expected_kernels(self, grouped=None):
+        """kernel launches of one step: decode, 2 assignment, 3 NMS (+1: the large-segment NMS
+        kernel, launched whenever the candidate capacity admits a segment above YH_BIG_MIN), and
+        the loss: dense + rows + finish, or per image range dense + rows, then one finish."""
+        grouped = (self.schedule == "grouped" and self._grad_ptrs is not None and self.B >= 8) \
+            if grouped is None else grouped
+        base = 6 + (1 if self.ws.key[3] > 4096 else 0)
+        if not grouped:
+            return base + 3
+        group = max(4, (int(os.environ.get("YH_GROUP", "8")) // 4) * 4)
+        R = (self.B + group - 1) // group
+        if R > 16:
+            group = ((self.B + 15) // 16 + 3) // 4 * 4
+            R = (self.B + group - 1) // group
+        return base + 2 * R + 1
 
     def run(self, heads: Sequence[torch.Tensor], gt_dev: torch.Tensor, off_dev: torch.Tensor, stream=None):
         """heads: L contiguous f32 CUDA tensors [B, A*(5+C), H, W]; gt_dev [G,5] f64; off_dev [B+1] i32.
@@ -186,6 +204,92 @@ class DeviceStep:
         main.wait_event(joins[0])
         main.wait_event(joins[2])
 
+    # -- the same step with the loss cut into L2-sized image groups ----------------------------
+    def run_grouped(self, heads, gt_dev, off_dev, publisher=None, group=None, dense_after=None):
+        r"""run_overlapped with the loss in RANGES of `group` images (yh_loss_*_range):
+
+            decode
+            nms_filter -> nms_segment -> nms_emit
+            assign ------------------\
+            dense(g0) -> dense(g1) -> ...        (main stream, the store stream)
+                 \-> rows(g0)  \-> rows(g1) ...  (side stream: rows of a group right behind its
+                                                  dense pass, gradients stored straight into the
+                                                  still-L2-resident lines)
+            ... -> finish_ranges (fixed-order reduction of the partial sums)
+
+        What this removes from the step: the staging buffer of the row gradients and the scatter
+        kernel that ran alone at the tail, re-reading from DRAM every line it touched
+        (loss_finish: 29 us, 18.6 MB read + 14.7 MB written for 4 MB of gradients, r1f)."""
+        main = torch.cuda.current_stream(self.dev)
+        if self._side is None:
+            self._side = [torch.cuda.Stream(self.dev), torch.cuda.Stream(self.dev, priority=-1),
+                          torch.cuda.Stream(self.dev, priority=-1)]
+        if getattr(self, "_rows_stream", None) is None:
+            self._rows_stream = torch.cuda.Stream(self.dev, priority=-1)
+        s_dec, s_asg, s_nms = self._side
+        s_rows = self._rows_stream
+        group = group or int(os.environ.get("YH_GROUP", "8"))
+        dense_after = dense_after or os.environ.get("YH_DENSE_AFTER", "assign")
+        group = max(4, (group // 4) * 4)
+        bounds = list(range(0, self.B, group)) + [self.B]
+        if len(bounds) - 1 > 16:
+            group = ((self.B + 15) // 16 + 3) // 4 * 4
+            bounds = list(range(0, self.B, group)) + [self.B]
+        R = len(bounds) - 1
+        hp = _lib.ptr_array(heads)
+        fork = torch.cuda.Event()
+        fork.record(main)
+        for st in self._side + [s_rows]:
+            st.wait_event(fork)
+        pub_done = None
+        if publisher is not None:
+            if self._pub_stream is None:
+                self._pub_stream = torch.cuda.Stream(self.dev)
+            self._pub_stream.wait_event(fork)
+            publisher.publish(self.losses4, self._pub_stream.cuda_stream)
+            pub_done = torch.cuda.Event()
+            pub_done.record(self._pub_stream)
+        self._assign(gt_dev, off_dev, s_asg.cuda_stream)
+        asg_done = torch.cuda.Event()
+        asg_done.record(s_asg)
+        self._nms(hp, s_nms.cuda_stream)
+        self._decode(hp, s_dec.cuda_stream)
+        s_rows.wait_event(asg_done)
+        if dense_after == "assign":
+            main.wait_event(asg_done)
+        img_off = self.lib.yh_assign_image_offsets(self.ws.handle)
+        for r in range(R):
+            lo, hi = bounds[r], bounds[r + 1]
+            _lib.check(self.lib.yh_loss_dense_range(self.ws.handle, hp, self.layers, self.L, self.B, self.C,
+                                                    lo, hi, r, R, self.cfg, self._grad_ptrs, main.cuda_stream))
+            ev = torch.cuda.Event()
+            ev.record(main)
+            s_rows.wait_event(ev)
+            _lib.check(self.lib.yh_loss_rows_range(
+                self.ws.handle, hp, self.layers, self.L, self.B, self.C, lo, hi, r, R,
+                self.m_batch.data_ptr(), self.m_flat.data_ptr(), self.m_target.data_ptr(),
+                self.m_class.data_ptr(), self.M.data_ptr(), self.mcap, img_off, self.cfg,
+                self.iou_score.data_ptr(), self.pred_rows.data_ptr(), self._grad_ptrs, s_rows.cuda_stream))
+        joins = []
+        for st in self._side + [s_rows]:
+            e = torch.cuda.Event()
+            e.record(st)
+            joins.append(e)
+        main.wait_event(joins[3])
+        if pub_done is not None:
+            main.wait_event(pub_done)
+        _lib.check(self.lib.yh_loss_finish_ranges(self.ws.handle, self.layers, self.L, self.B, self.C, R,
+                                                  self.M.data_ptr(), self.mcap, self.cfg,
+                                                  self.losses4.data_ptr(), main.cuda_stream))
+        for k in (0, 1, 2):
+            main.wait_event(joins[k])
+
+    def _step(self, heads, gt_dev, off_dev, publisher=None):
+        if self.schedule == "grouped" and self._grad_ptrs is not None and self.B >= 8:
+            self.run_grouped(heads, gt_dev, off_dev, publisher=publisher)
+        else:
+            self.run_overlapped(heads, gt_dev, off_dev, publisher=publisher)
+
     def capture(self, heads, gt_dev, off_dev, loss_slots: int = 1, publisher=None):
         """Captures `run_overlapped` on these buffers into a CUDA graph; `replay()` launches it.
         The captured pointers are those of `heads`/`gt_dev`/`off_dev`: refill them in place.
@@ -199,7 +303,7 @@ class DeviceStep:
         STEP BEHIND (replay i publishes the scalars of replay i-1, under replay i's kernels):
         call `publisher.publish(step.losses4)` once after the last replay to flush."""
         self._keep = (list(heads), gt_dev, off_dev)
-        self.run_overlapped(heads, gt_dev, off_dev)  # warm: module attributes, streams
+        self._step(heads, gt_dev, off_dev)  # warm: module attributes, streams
         torch.cuda.synchronize(self.dev)
         # [total, iou, cls, obj, 1] per slot; `weighted5` = that times the local batch size, the
         # operand of the data-parallel weighted mean (multi_gpu.rs:188-195), produced in-graph
@@ -215,7 +319,7 @@ class DeviceStep:
             g = torch.cuda.CUDAGraph()
             before = int(self.lib.yh_launch_count(0))
             with torch.cuda.graph(g, stream=cap):
-                self.run_overlapped(heads, gt_dev, off_dev, publisher=publisher)
+                self._step(heads, gt_dev, off_dev, publisher=publisher)
                 if publisher is None and loss_slots > 1:
                     torch.mul(self._l5_ring[k], float(self.B), out=self._w5_ring[k])
             self.kernels_in_graph = int(self.lib.yh_launch_count(0)) - before
