@@ -244,8 +244,16 @@ const int32_t* yh_assign_image_offsets(const YhWorkspace* ws);
  * compare, nms.rs:97-99); group = batch (by_class=0) or batch*C+class (nms.rs:129-133).
  * Greedy rule (oracle/nms.py, the stand-in for the un-vendored tch-nms): candidates in
  * score-descending order, equal scores in nonzero() order (class*N+instance ascending); a
- * candidate is dropped iff a kept box of its group has IoU > iou_threshold.  NMS is global per
- * image: the reference's 65536-row chunking (nms.rs:135-151) is NOT reproduced.
+ * candidate is dropped iff a kept box of its group has IoU > iou_threshold.
+ * DEVIATION (SURVEY.md §8b lists a `compat_chunk65536` flag for this export; there is none): above
+ * 65 536 candidates per batch the reference cuts the (batch, class, instance)-ordered rows into
+ * independent 65 536-row chunks, runs tch-nms on each and then gathers with the CHUNK-LOCAL indices
+ * (nms.rs:135-160: the chunk offset is never added) — the rows it returns past the first chunk are
+ * not the rows NMS kept.  That result is not reproduced: yh_nms runs ONE global NMS per image (per
+ * image and class with suppress_by_class) for any number of candidates, which is what the chunk
+ * loop approximates and equals it exactly whenever the batch has <= 65 536 candidates.  The
+ * chunk-wise variant (with the offset repaired) exists only in the oracle (oracle/nms.py,
+ * `compat_chunk65536`) to document the difference.
  * Kept rows are emitted ordered by (batch, score desc, class*N+instance asc):
  *   kb/kc/ki  i64 batches/classes/instances ; tlbr [cap,4] f32 (t,l,b,r) ; conf [cap]
  *   out_K_dev int32 count (device), clamped to capacity (overflow -> yh_read_counts error).

@@ -227,3 +227,16 @@ def test_integration_md_rust_block_matches_header():
         return 0 if a in ("", "void") else a.count(",") + 1
     for f in c_fns:
         assert nargs(c_fns[f]) == nargs(rust_fns[f]) == len(_lib.SYMBOLS[f][1]), f
+
+
+def test_c_program_fails_loudly_without_a_gpu():
+    """tests/c/abi_smoke.c is a plain-C caller of the ABI (gcc -std=c99, no Python, no
+    torch).  On a machine without a CUDA device its first compute-side call must fail with the
+    library's own message (exit code 2); on the GPU box tests/test_gpu_abi_c.py runs it to the end."""
+    exe = os.path.join(ROOT, "tests", "c", "abi_smoke")
+    assert os.path.exists(exe), "build it: make -C yolo_dl_b200/csrc abi_smoke"
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present: covered by the gpu-marked run")
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 2, (r.returncode, r.stdout, r.stderr)
+    assert "no CPU fallback" in r.stderr
