@@ -369,10 +369,14 @@ int64_t yh_launch_count(int reset);
  * and the launch count since the last read. */
 #define YH_NUM_KERNELS 16
 int yh_timing_enable(int on);
-/* Debug aid: while dev_buf (2 * number-of-kernel-ids uint64, device) is set on this thread, every
- * launch is bracketed by one-thread kernels that write %globaltimer (ns) to dev_buf[2*id] and
- * dev_buf[2*id+1]; capturable into a CUDA graph.  NULL disables. */
-int yh_trace_enable(unsigned long long* dev_buf);
+/* Debug aid: while dev_buf (2 * capacity uint64, device) is set on this thread, launch number i
+ * since the call (in issue order, i < capacity) is bracketed by one-thread kernels that write
+ * %globaltimer (ns) to dev_buf[2*i] and dev_buf[2*i+1]; capturable into a CUDA graph, so it shows
+ * where every kernel really runs inside an overlapped, replayed step.  NULL disables.
+ * yh_trace_ids copies the kernel id (order of yh_timing_read) of the first n traced launches and
+ * returns how many launches were issued while tracing was on. */
+int yh_trace_enable(unsigned long long* dev_buf, int capacity);
+int yh_trace_ids(int32_t* ids, int n);
 int yh_timing_read(double* ms_sum, int64_t* launches, int n);
 
 #ifdef __cplusplus

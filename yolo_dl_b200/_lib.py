@@ -103,7 +103,8 @@ SYMBOLS = {
     "yh_workspace_candidates_needed": (c_int, [c_void_p]),
     "yh_launch_count": (c_int64, [c_int]),
     "yh_timing_enable": (c_int, [c_int]),
-    "yh_trace_enable": (c_int, [c_void_p]),
+    "yh_trace_enable": (c_int, [c_void_p, c_int]),
+    "yh_trace_ids": (c_int, [POINTER(c_int32), c_int]),
     "yh_timing_read": (c_int, [POINTER(c_double), POINTER(c_int64), c_int]),
 }
 

@@ -45,7 +45,8 @@ static cudaEvent_t get_event() {
 // graph, so it shows where each kernel really runs inside the overlapped, replayed step
 // (tools/timeline.py).  Debug aid only.
 static thread_local unsigned long long* g_trace = nullptr;
-static thread_local int g_trace_id = 0;
+static thread_local int g_trace_cap = 0;
+static thread_local std::vector<int>* g_trace_ids = nullptr;  // kernel id of every traced launch
 
 __global__ void stamp_kernel(unsigned long long* slot) {
   unsigned long long t;
@@ -55,8 +56,14 @@ __global__ void stamp_kernel(unsigned long long* slot) {
 
 void timing_begin(int id, cudaStream_t s) {
   if (g_trace) {
-    g_trace_id = id;
-    stamp_kernel<<<1, 1, 0, s>>>(g_trace + 2 * id);
+    // one slot per LAUNCH, in issue order (a ranged loss launches the same kernel several times)
+    if (!g_trace_ids) g_trace_ids = new std::vector<int>();
+    if ((int)g_trace_ids->size() < g_trace_cap) {
+      stamp_kernel<<<1, 1, 0, s>>>(g_trace + 2 * g_trace_ids->size());
+      g_trace_ids->push_back(id);
+    } else {
+      g_trace_ids->push_back(-1 - id);  // over capacity: counted, not stamped
+    }
     return;
   }
   if (!g_timing) return;
@@ -71,7 +78,8 @@ void timing_begin(int id, cudaStream_t s) {
 
 void timing_end(cudaStream_t s) {
   if (g_trace) {
-    stamp_kernel<<<1, 1, 0, s>>>(g_trace + 2 * g_trace_id + 1);
+    if (g_trace_ids && !g_trace_ids->empty() && g_trace_ids->back() >= 0)
+      stamp_kernel<<<1, 1, 0, s>>>(g_trace + 2 * (g_trace_ids->size() - 1) + 1);
     return;
   }
   if (!g_timing || !g_timed || g_timed->empty()) return;
@@ -149,9 +157,17 @@ int64_t yh_launch_count(int reset) {
   return v;
 }
 
-int yh_trace_enable(unsigned long long* dev_buf) {
+int yh_trace_enable(unsigned long long* dev_buf, int capacity) {
   yh::g_trace = dev_buf;
+  yh::g_trace_cap = dev_buf ? capacity : 0;
+  if (dev_buf && yh::g_trace_ids) yh::g_trace_ids->clear();
   return YH_OK;
+}
+
+int yh_trace_ids(int32_t* ids, int n) {
+  const int have = yh::g_trace_ids ? (int)yh::g_trace_ids->size() : 0;
+  for (int i = 0; i < n && i < have; ++i) ids[i] = (*yh::g_trace_ids)[i];
+  return have;
 }
 
 int yh_timing_enable(int on) {
