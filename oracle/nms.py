@@ -85,26 +85,26 @@ def nms_forward(merged: dict, conf_thr: float, iou_thr: float, by_class: bool,
         group = batches * C + classes if by_class else batches.clone()
         # everything up to here is the reference's ATen op sequence and runs on whatever device
         # `merged` lives on (CPU, or CUDA = the reference's real deployment through libtorch);
-        # the greedy stand-in for tch-nms below works on host copies of its inputs
+        # the greedy stand-in for tch-nms works on host copies of its inputs, torchvision's
+        # batched_nms (use_torchvision) on the tensors where they are
+        chunk = 65536 if compat_chunk65536 else max(K, 1)
+        tv_keeps = None
+        if use_torchvision and K > 0:
+            import torchvision
+            tv_keeps = [torchvision.ops.batched_nms(ltrb[s:s + chunk], conf[s:s + chunk].view(-1),
+                                                    group[s:s + chunk], float(iou_thr)).cpu().numpy() + s
+                        for s in range(0, K, chunk)]
         tlbr_t = torch.cat([new_t, new_l, new_b, new_r], 1).cpu()
         ltrb, conf, group = ltrb.cpu(), conf.cpu(), group.cpu()
         batches, classes, instances = batches.cpu(), classes.cpu(), instances.cpu()
         if K == 0:
             keep = np.zeros(0, dtype=np.int64)
+        elif tv_keeps is not None:
+            keep = np.concatenate(tv_keeps)
         else:
-            chunk = 65536 if compat_chunk65536 else K
-            keeps = []
-            for s in range(0, K, chunk):
-                e = min(s + chunk, K)
-                if use_torchvision:
-                    import torchvision
-                    k = torchvision.ops.batched_nms(ltrb[s:e], conf[s:e].view(-1), group[s:e],
-                                                    float(iou_thr)).numpy()
-                else:
-                    k = nms_by_scores(ltrb[s:e].numpy(), conf[s:e].view(-1).numpy(),
-                                      group[s:e].numpy(), iou_thr)
-                keeps.append(k + s)
-            keep = np.concatenate(keeps)
+            keep = np.concatenate([nms_by_scores(ltrb[s:s + chunk].numpy(), conf[s:s + chunk].view(-1).numpy(),
+                                                 group[s:s + chunk].numpy(), iou_thr) + s
+                                   for s in range(0, K, chunk)])
         kb = batches.numpy()[keep]
         kc = classes.numpy()[keep]
         ki = instances.numpy()[keep]

@@ -71,11 +71,17 @@ class DeviceStep:
         self.schedule = os.environ.get("YH_SCHEDULE", "grouped")
         self.kernels_in_graph = 0
 
-    def algorithmic_bytes(self):
-        """SURVEY.md §8d per-image figures x batch, per kernel (M-dependent part excluded)."""
+    def algorithmic_bytes(self, matches=0, obj_pass=0, detections=0):
+        """SURVEY.md §8d algorithmic bytes of one launch of every kernel of the step (whole batch):
+        decode 32·N·B; dense loss 344·N·B (4 read + 340 written); matched rows 340·M read and
+        340·M written (scatter); candidate filter 4·N·B (objectness plane) + 32-byte sectors of
+        the C class logits of the `obj_pass` instances that pass the objectness test — NOT the
+        340·N·B of the reference's traffic; NMS 24·K' in + 8·K out."""
         n = self.N * self.B
-        return {"decode_kernel": 32 * n, "loss_dense_kernel": 344 * n, "nms_filter_kernel": 340 * n}
-
+        return {"decode_kernel": 32 * n, "loss_dense_kernel": 344 * n,
+                "loss_rows_kernel": 340 * matches, "loss_finish_kernel": 340 * matches,
+                "nms_filter_kernel": 4 * n + 32 * self.C * obj_pass,
+                "nms_segment_kernel": 24 * detections, "nms_emit_kernel": 32 * detections}
 
     def expected_kernels(self, grouped=None):
         """kernel launches of one step: decode, 2 assignment, 3 NMS (+1: the large-segment NMS
