@@ -599,6 +599,52 @@ def run_native(args):
     except Exception as e:
         roofline["in_graph"] = {"unavailable": repr(e)[:200]}
 
+    # ---- f3: the data-parallel gradient all-reduce either side of the path (N > 1) ---------------
+    # What replaces sync_weights + the to_device fan-in through GPU 0 (multi_gpu.rs:503-530,656-726):
+    # a bucketed NCCL all-reduce of a YOLOv4-sized parameter set (64 M f32 = 256 MB), alone and on
+    # its own stream under the replayed step graph — the one real collective of a training step.
+    dp_allreduce = None
+    if world > 1:
+        from yolo_dl_b200 import dp
+        params = [torch.zeros(4 << 20, device=dev, requires_grad=True) for _ in range(16)]
+        gar = dp.GradientAllReduce(params, bucket_bytes=64 << 20)
+        nbytes = gar.nbytes()
+        for _ in range(3):
+            gar.reduce(B, B * world)
+        barrier()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps_ar = 10
+        a0.record()
+        for _ in range(reps_ar):
+            gar.reduce(B, B * world)
+        a1.record()
+        barrier()
+        ar_ms = a0.elapsed_time(a1) / reps_ar
+        # under the step: all-reduce on a side stream, the step graph on the current one
+        side = torch.cuda.Stream(dev)
+        Ko = max(10, min(K, 100))
+        barrier()
+        o0, o1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        o0.record()
+        for _ in range(Ko):
+            side.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side):
+                gar.reduce(B, B * world)
+            step.replay()
+            torch.cuda.current_stream(dev).wait_stream(side)
+        o1.record()
+        barrier()
+        both_ms = o0.elapsed_time(o1) / Ko
+        t = torch.tensor([ar_ms, both_ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ar_ms, both_ms = float(t[0]), float(t[1])
+        dp_allreduce = {"bytes": nbytes, "buckets": len(gar.buckets), "ms_alone": ar_ms,
+                        "busbw_GBps": 2.0 * (world - 1) / world * nbytes / (ar_ms * 1e-3) / 1e9,
+                        "ms_step_plus_allreduce_overlapped": both_ms, "ms_step_alone": ms / K,
+                        "nvlink5_per_direction_GBps": 900,
+                        "what": "dp.GradientAllReduce (NCCL, PreMulSum B_local/B) of 64 M f32 in 64 MB buckets"}
+        del gar, params
+
     # ---- strong scaling: the literal BASELINE configs[1], ONE global batch of 64 over the N GPUs ----
     strong = None
     if not args.no_strong:
@@ -737,7 +783,7 @@ def run_native(args):
                 "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f32", "data": "synthetic", "config": workload_config(args, world),
                 "value_windows": value_windows, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
-                "strong": strong, "gpu_launches": launches,
+                "strong": strong, "dp_gradient_allreduce": dp_allreduce, "gpu_launches": launches,
                 "execution": f"CUDA graph of {step.kernels_in_graph} kernels on forked/joined streams "
                              f"(schedule: {step.schedule}), replayed once per step",
                 "sequential_ms_per_step": seq_ms, "loss_exchange": exchange, "other_configs": extras,
