@@ -84,6 +84,8 @@ assign_slots_kernel(const AssignTab t, const double* __restrict__ gt,
   __shared__ double s_gt[kMaxGtSmem][4];
   __shared__ unsigned s_bits[kBitsSmem];
   __shared__ int s_cnt[kAssignThreads / 32];
+  griddep_launch();
+  griddep_wait();
   const int b = blockIdx.x;
   const int g0 = gt_off[b], g1 = gt_off[b + 1];
   const int ng = g1 - g0;
@@ -169,6 +171,8 @@ assign_emit_kernel(int N, int B, const int words, const double* __restrict__ gt,
   __shared__ int s_warp[kEmitThreads / 32];
   __shared__ int s_base;
   __shared__ int s_list[kEmitList];
+  griddep_launch();
+  griddep_wait();
   const int b = blockIdx.x;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
 
@@ -311,11 +315,10 @@ extern "C" int yh_assign(YhWorkspace* ws, const double* gt_dev, const int32_t* g
                                                    ws->img_count);
   YH_LAUNCHED(s);
   YH_TIME(YH_K_ASSIGN_EMIT, s);
-  assign_emit_kernel<<<B, kEmitThreads, 0, s>>>(
-      t.N, B, words, gt_dev, gt_offsets_dev, ws->slot_dist, ws->slot_gt, ws->slot_bits,
-      ws->img_count, (long long*)out_batch,
-      (long long*)out_flat, out_gt, out_target, (long long*)out_class, out_M_dev, capacity,
-      ws->err_flag, ws->img_off);
+  YH_CUDA(launch_pdl(assign_emit_kernel, dim3(B), dim3(kEmitThreads), 0, s, t.N, B, words, gt_dev,
+                     gt_offsets_dev, ws->slot_dist, ws->slot_gt, ws->slot_bits, ws->img_count,
+                     (long long*)out_batch, (long long*)out_flat, out_gt, out_target,
+                     (long long*)out_class, out_M_dev, capacity, ws->err_flag, ws->img_off));
   YH_LAUNCHED(s);
   return YH_OK;
 }

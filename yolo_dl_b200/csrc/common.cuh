@@ -59,6 +59,37 @@ void timing_end(cudaStream_t s);
   } while (0)
 
 // ---------------------------------------------------------------------------------
+// programmatic dependent launch (PDL) along the two dependent chains of the step
+//   assign_slots -> assign_emit -> loss_rows -> loss_finish     nms_filter -> nms_segment -> nms_emit
+// Every kernel of a chain calls griddep_launch() first thing (the NEXT kernel of the stream may then
+// be scheduled as soon as all CTAs of this one have started) and griddep_wait() before it touches
+// global memory (blocks until the PREVIOUS kernel of the stream has completed and flushed).  With
+// the launch attribute of launch_pdl the ~2-4 us launch + drain gap between dependent kernels — most
+// of the step at 8 images per GPU — overlaps the predecessor's execution; without the attribute both
+// instructions are no-ops and the stream serialises as usual.  Capturable into CUDA graphs.
+// ---------------------------------------------------------------------------------
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+bool pdl_enabled();  // YH_PDL=0 turns the attribute off (A/B)
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                              cudaStream_t s, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
+// ---------------------------------------------------------------------------------
 // layer table (kernel parameter, by value)
 // ---------------------------------------------------------------------------------
 struct LayerTab {

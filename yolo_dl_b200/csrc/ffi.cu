@@ -1,6 +1,7 @@
 // ffi.cu — workspace, error string, counters: the non-kernel part of the C ABI.
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -19,6 +20,14 @@ void set_error(const char* fmt, ...) {
 }
 
 int64_t& launch_counter() { return g_launches; }
+
+bool pdl_enabled() {
+  static const bool on = []() {
+    const char* e = getenv("YH_PDL");
+    return !(e && e[0] == '0');
+  }();
+  return on;
+}
 
 // ---- optional per-launch timing: one CUDA event pair per launch, on the launch stream ----
 struct TimedLaunch {

@@ -524,6 +524,8 @@ loss_rows_kernel(const LayerTab t, const GradTab g, const LossParams p, const Ro
                  const int* __restrict__ M_dev, const int capacity,
                  float* __restrict__ iou_score, float* __restrict__ pred_rows,
                  float* __restrict__ row_grad, double* __restrict__ partials) {
+  griddep_launch();
+  griddep_wait();
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int warps = kRowThreads / 32;
   const int M = min(*M_dev, capacity);
@@ -767,6 +769,8 @@ loss_finish_kernel(const LayerTab t, const GradTab g, const LossParams p,
                    const int dense_per_range, const int rows_per_range, const int num_ranges,
                    const int range_stride, float* __restrict__ losses4,
                    int* __restrict__ err_flag) {
+  griddep_launch();
+  griddep_wait();
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int warps = kFinishThreads / 32;
   const int M = min(*M_dev, capacity);
@@ -1109,10 +1113,10 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
     memset(&rg, 0, sizeof(rg));
     if (direct) rg = g;
     YH_TIME(YH_K_LOSS_ROWS, s);
-    loss_rows_kernel<<<row_grid, kRowThreads, 0, s>>>(
-        tab, rg, p, rr, (const long long*)m_batch, (const long long*)m_flat, m_target,
-        (const long long*)m_class, M_dev, capacity, iou_score_dev, pred_rows_dev,
-        (want_grad && !direct) ? ws->row_grad : nullptr, ws->partials);
+    YH_CUDA(launch_pdl(loss_rows_kernel, dim3(row_grid), dim3(kRowThreads), 0, s, tab, rg, p, rr,
+                       (const long long*)m_batch, (const long long*)m_flat, m_target,
+                       (const long long*)m_class, M_dev, capacity, iou_score_dev, pred_rows_dev,
+                       (want_grad && !direct) ? ws->row_grad : nullptr, ws->partials));
     YH_LAUNCHED(s);
   }
   if (phases & kPhaseFinish) {
@@ -1122,10 +1126,11 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
       if (fin_grid > ws->num_sms * 8) fin_grid = ws->num_sms * 8;
     }
     YH_TIME(YH_K_LOSS_FINISH, s);
-    loss_finish_kernel<<<fin_grid, kFinishThreads, 0, s>>>(
-        tab, g, p, (const long long*)m_batch, (const long long*)m_flat, M_dev, capacity,
-        grad_heads ? ws->row_grad : nullptr, ws->partials, dense_grid, row_grid, num_ranges,
-        kRangeSlots, losses4_dev, ws->err_flag);
+    YH_CUDA(launch_pdl(loss_finish_kernel, dim3(fin_grid), dim3(kFinishThreads), 0, s, tab, g, p,
+                       (const long long*)m_batch, (const long long*)m_flat, M_dev, capacity,
+                       grad_heads ? (const float*)ws->row_grad : (const float*)nullptr,
+                       (const double*)ws->partials, dense_grid, row_grid, num_ranges, kRangeSlots,
+                       losses4_dev, ws->err_flag));
     YH_LAUNCHED(s);
   }
   return YH_OK;

@@ -132,6 +132,7 @@ __global__ void __launch_bounds__(kFilterThreads)
 nms_filter_kernel(const LayerTab t, const float thr, unsigned long long* __restrict__ keys,
                   const int stride, const int cap, int* __restrict__ count,
                   int* __restrict__ err_flag) {
+  griddep_launch();  // nms_segment_kernel's CTAs may take their places while the filter runs
   const int b = blockIdx.y;
   const int lane = threadIdx.x & 31;
   const float* hp[kFilterPer];
@@ -323,6 +324,8 @@ nms_segment_kernel(const P prov, const SegView v, const double iou_thr) {
   __shared__ unsigned s_keep[32];
   static_assert(kNmsThreads == 2 * kTile, "two threads per candidate of a tile");
 
+  griddep_launch();
+  griddep_wait();
   const int seg = blockIdx.x;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int found = v.count[seg];  // reset to 0 by the emit / rank kernel that follows
@@ -818,6 +821,8 @@ nms_emit_kernel(const SegView v, const int S, const int N, long long* __restrict
                 int* __restrict__ out_K, const int capacity, int* __restrict__ err_flag) {
   __shared__ int s_warp[8];
   __shared__ int s_base;
+  griddep_launch();
+  griddep_wait();
   const int seg = blockIdx.x;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   int part = 0;
@@ -1089,7 +1094,7 @@ static int launch_segments(YhWorkspace* ws, const P& prov, SegView v, int S, dou
   const bool big = ws->big_box != nullptr && v.cap > kBigMin;
   v.big_min = big ? kBigMin : 0;
   YH_TIME(YH_K_NMS_SEGMENT, s);
-  nms_segment_kernel<P><<<S, kNmsThreads, smem, s>>>(prov, v, iou_thr);
+  YH_CUDA(launch_pdl(nms_segment_kernel<P>, dim3(S), dim3(kNmsThreads), smem, s, prov, v, iou_thr));
   YH_LAUNCHED(s);
   if (!big) return YH_OK;
   // the multi-CTA kernel: one CTA per SM, co-resident (cooperative launch: its groups spin on
@@ -1192,9 +1197,16 @@ int yh_nms(YhWorkspace* ws, const float* const* heads, const YhLayer* layers, in
   rc = launch_segments(ws, prov, v, B, iou_threshold, s);
   if (rc) return rc;
   YH_TIME(YH_K_NMS_EMIT, s);
-  nms_emit_kernel<<<B, 256, 0, s>>>(v, B, prov.t.N, (long long*)kb, (long long*)kc,
-                                    (long long*)ki, tlbr, conf, nullptr, out_K_dev, capacity,
-                                    ws->err_flag);
+  if (ws->big_box != nullptr && v.cap > kBigMin) {
+    // behind the cooperative large-segment kernel: plain launch
+    nms_emit_kernel<<<B, 256, 0, s>>>(v, B, prov.t.N, (long long*)kb, (long long*)kc,
+                                      (long long*)ki, tlbr, conf, nullptr, out_K_dev, capacity,
+                                      ws->err_flag);
+  } else {
+    YH_CUDA(launch_pdl(nms_emit_kernel, dim3(B), dim3(256), 0, s, v, B, prov.t.N, (long long*)kb,
+                       (long long*)kc, (long long*)ki, tlbr, conf, (long long*)nullptr, out_K_dev,
+                       capacity, ws->err_flag));
+  }
   YH_LAUNCHED(s);
   return YH_OK;
 }
