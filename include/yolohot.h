@@ -307,13 +307,18 @@ int yh_match_det_gt(const double* dets_tlbr_dev, const int32_t* det_offsets_dev,
  * out_ap_dev is [num_problems, num_thresholds] f64; MeanApCalculator::compute_mean_ap (:252-275)
  * is the mean of a row.  Detections of equal confidence are ordered by (ground truth ascending,
  * none first; IoU descending; index) — the reference iterates a HashMap there (unspecified).
- * max_detections_per_problem <= 8192; n_points in 2..1024 (COCO: 101).  An empty problem yields 0
- * (the reference panics, :90). */
+ * n_points in 2..1024 (COCO: 101).  An empty problem yields 0 (the reference panics, :90).
+ * Any number of detections per problem (the reference's Vec code has no bound, :157-219): up to
+ * 8192 the per-detection arrays live in shared memory; above, in `scratch_dev` (device memory,
+ * 16-byte aligned, yh_average_precision_scratch_bytes(num_problems, max_detections_per_problem)
+ * bytes, which is 0 when no scratch is needed; too little scratch -> YH_ERR_CAPACITY). */
+size_t yh_average_precision_scratch_bytes(int num_problems, int max_detections_per_problem);
 int yh_average_precision(const int32_t* det_gt_dev, const double* det_iou_dev,
                          const double* det_conf_dev, const int32_t* problem_offsets_dev,
                          const int32_t* num_ground_truth_dev, int num_problems,
                          int max_detections_per_problem, const double* iou_thresholds_dev,
-                         int num_thresholds, int n_points, double* out_ap_dev, void* stream);
+                         int num_thresholds, int n_points, double* out_ap_dev, void* scratch_dev,
+                         size_t scratch_bytes, void* stream);
 
 /* ---- §8e: the data-parallel loss exchange as peer-memory stores over NVLink / NVSwitch.
  * Replaces the per-step master-device averaging of the loss scalars

@@ -107,12 +107,15 @@ def test_match_det_gt_segment_without_ground_truth(dev):
     assert m.ground_truth.tolist() == [-1] and m.iou.tolist() == [0.0]
 
 
-@pytest.mark.parametrize("seed,P,dmax", [(0, 1, 50), (1, 12, 400), (2, 80, 90), (3, 2, 8192), (4, 5, 1)])
+@pytest.mark.parametrize("seed,P,dmax", [(0, 1, 50), (1, 12, 400), (2, 80, 90), (3, 2, 8192), (4, 5, 1),
+                                         (5, 3, 8193), (6, 2, 30000)])
 def test_average_precision_random_equals_oracle(dev, seed, P, dmax):
+    """seeds 5, 6: more than 8192 detections in one problem (a COCO-val "person" class): the
+    per-detection arrays move from shared memory to the caller's scratch, same bits out."""
     rng = np.random.default_rng(100 + seed)
     sel, iou, conf, offs, ngt = [], [], [], [0], []
     for p in range(P):
-        nd = dmax if (seed == 3 and p == 0) else int(rng.integers(1, dmax + 1))
+        nd = dmax if (seed in (3, 5, 6) and p == 0) else int(rng.integers(1, dmax + 1))
         g = int(rng.integers(1, 40))
         s = rng.integers(-1, g, nd)
         v = np.where(s < 0, 0.0, rng.uniform(0.05, 1.0, nd))
@@ -149,6 +152,18 @@ def test_evaluation_argument_validation(dev):
         yev.ApCalculator(yev.IntegralMethod(0))
     with pytest.raises(ValueError):
         yev.MeanApCalculator(yev.IntegralMethod(101), [])
+    # more than 8192 detections without scratch: refused with the size to pass, not computed wrongly
+    from yolo_dl_b200 import _lib
+    lib = _lib.load()
+    assert lib.yh_average_precision_scratch_bytes(4, 8192) == 0
+    need = lib.yh_average_precision_scratch_bytes(1, 9000)
+    assert need >= 9000 * 17
     m = dmatch(dev, [0] * 9000, [0.5] * 9000)
-    with pytest.raises(Exception):
-        yev.ApCalculator.new_coco().compute_by_detections(m, torch.zeros(9000, device=dev), 3, 0.5)
+    cf = torch.zeros(9000, dtype=torch.float64, device=dev)
+    off = torch.tensor([0, 9000], dtype=torch.int32, device=dev)
+    ng = torch.tensor([3], dtype=torch.int32, device=dev)
+    th = torch.tensor([0.5], dtype=torch.float64, device=dev)
+    out = torch.zeros(1, dtype=torch.float64, device=dev)
+    rc = lib.yh_average_precision(m.ground_truth.data_ptr(), m.iou.data_ptr(), cf.data_ptr(), off.data_ptr(),
+                                  ng.data_ptr(), 1, 9000, th.data_ptr(), 1, 101, out.data_ptr(), None, 0, None)
+    assert rc == _lib.YH_ERR_CAPACITY and b"scratch" in lib.yh_last_error()

@@ -201,8 +201,9 @@ __global__ void __launch_bounds__(kApThreads)
 ap_kernel(const int* __restrict__ det_gt, const double* __restrict__ det_iou,
           const double* __restrict__ det_conf, const int* __restrict__ prob_off,
           const int* __restrict__ num_gt, const double* __restrict__ thresholds, const int T,
-          const int n_points, double* __restrict__ out_ap) {
-  extern __shared__ __align__(16) unsigned char smem[];
+          const int n_points, double* __restrict__ out_ap, unsigned char* __restrict__ scratch,
+          const size_t scratch_per_problem) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
   const int p = blockIdx.x;
   const int d0 = prob_off[p], D = prob_off[p + 1] - d0;
   if (D <= 0) {  // the reference panics on an empty curve (average_precision.rs:90); 0 here
@@ -211,12 +212,17 @@ ap_kernel(const int* __restrict__ det_gt, const double* __restrict__ det_iou,
   }
   int P = 2;
   while (P < D) P <<= 1;
-  double* env = reinterpret_cast<double*>(smem);
-  double* s_dpart = env + P;                       // kApThreads doubles (also the point values)
-  int* idx = reinterpret_cast<int*>(s_dpart + kApThreads);
+  // the scan partials always live in shared memory; the four per-detection arrays too when the
+  // problem fits (<= kApMax detections), else in this problem's slice of the caller's scratch
+  // (L2-resident; the same code walks either through generic pointers)
+  double* s_dpart = reinterpret_cast<double*>(smem_raw);  // kApThreads doubles (also the point values)
+  int* s_ipart = reinterpret_cast<int*>(s_dpart + kApThreads);  // kApThreads ints
+  unsigned char* arrays = (P <= kApMax) ? reinterpret_cast<unsigned char*>(s_ipart + kApThreads)
+                                        : scratch + (size_t)p * scratch_per_problem;
+  double* env = reinterpret_cast<double*>(arrays);
+  int* idx = reinterpret_cast<int*>(env + P);
   int* tp = idx + P;
-  int* s_ipart = tp + P;                           // kApThreads ints
-  unsigned char* best = reinterpret_cast<unsigned char*>(s_ipart + kApThreads);
+  unsigned char* best = reinterpret_cast<unsigned char*>(tp + P);
 
   ApView v;
   v.gt = det_gt + d0;
@@ -296,9 +302,17 @@ ap_kernel(const int* __restrict__ det_gt, const double* __restrict__ det_iou,
   }
 }
 
+// env f64[P] | idx i32[P] | tp i32[P] | best u8[P], rounded to 16 bytes
+static size_t ap_array_bytes(int P) {
+  return (((size_t)P * (sizeof(double) + 2 * sizeof(int) + 1)) + 15) & ~(size_t)15;
+}
 static size_t ap_smem_bytes(int P) {
-  return (size_t)P * sizeof(double) + kApThreads * sizeof(double) + 2 * (size_t)P * sizeof(int) +
-         kApThreads * sizeof(int) + (size_t)P;
+  return kApThreads * (sizeof(double) + sizeof(int)) + (P <= kApMax ? ap_array_bytes(P) : 0);
+}
+static int ap_pow2(int d) {
+  int P = 2;
+  while (P < d) P <<= 1;
+  return P;
 }
 
 }  // namespace yh
@@ -326,23 +340,36 @@ int yh_match_det_gt(const double* dets_tlbr_dev, const int32_t* det_offsets_dev,
   return YH_OK;
 }
 
+size_t yh_average_precision_scratch_bytes(int num_problems, int max_detections_per_problem) {
+  if (num_problems < 1 || max_detections_per_problem <= yh::kApMax) return 0;
+  return (size_t)num_problems * yh::ap_array_bytes(yh::ap_pow2(max_detections_per_problem));
+}
+
 int yh_average_precision(const int32_t* det_gt_dev, const double* det_iou_dev,
                          const double* det_conf_dev, const int32_t* problem_offsets_dev,
                          const int32_t* num_ground_truth_dev, int num_problems,
                          int max_detections_per_problem, const double* iou_thresholds_dev,
-                         int num_thresholds, int n_points, double* out_ap_dev, void* stream) {
+                         int num_thresholds, int n_points, double* out_ap_dev, void* scratch_dev,
+                         size_t scratch_bytes, void* stream) {
   using namespace yh;
   YH_REQUIRE(num_problems >= 1 && num_thresholds >= 1, "num_problems=%d num_thresholds=%d",
              num_problems, num_thresholds);
   // ApCalculator::new (:72-84); a single point divides by n_points-1 = 0 in the reference
   YH_REQUIRE(n_points >= 2 && n_points <= kApThreads, "invalid number of interpolated points %d",
              n_points);
-  YH_REQUIRE(max_detections_per_problem >= 0 && max_detections_per_problem <= kApMax,
-             "%d detections in one problem > %d", max_detections_per_problem, kApMax);
+  YH_REQUIRE(max_detections_per_problem >= 0 && max_detections_per_problem <= (1 << 30),
+             "max_detections_per_problem=%d", max_detections_per_problem);
   YH_REQUIRE(problem_offsets_dev && num_ground_truth_dev && iou_thresholds_dev && out_ap_dev,
              "NULL argument");
-  int P = 2;
-  while (P < max_detections_per_problem) P <<= 1;
+  const int P = ap_pow2(max_detections_per_problem);
+  const size_t need = yh_average_precision_scratch_bytes(num_problems, max_detections_per_problem);
+  if (need > 0 && (scratch_dev == nullptr || scratch_bytes < need)) {
+    set_error("%d detections in one problem exceed the %d held in shared memory: pass %zu bytes of "
+              "device scratch (yh_average_precision_scratch_bytes), got %zu",
+              max_detections_per_problem, kApMax, need, scratch_dev ? scratch_bytes : (size_t)0);
+    return YH_ERR_CAPACITY;
+  }
+  YH_REQUIRE(need == 0 || ((uintptr_t)scratch_dev & 15) == 0, "scratch not 16-byte aligned");
   const size_t smem = ap_smem_bytes(P);
   cudaStream_t s = (cudaStream_t)stream;
   YH_CUDA(cudaFuncSetAttribute(ap_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -350,7 +377,8 @@ int yh_average_precision(const int32_t* det_gt_dev, const double* det_iou_dev,
   ap_kernel<<<num_problems, kApThreads, smem, s>>>(det_gt_dev, det_iou_dev, det_conf_dev,
                                                    problem_offsets_dev, num_ground_truth_dev,
                                                    iou_thresholds_dev, num_thresholds, n_points,
-                                                   out_ap_dev);
+                                                   out_ap_dev, (unsigned char*)scratch_dev,
+                                                   need ? ap_array_bytes(P) : (size_t)0);
   YH_LAUNCHED(s);
   return YH_OK;
 }

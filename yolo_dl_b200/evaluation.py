@@ -92,11 +92,13 @@ class ApCalculator:
         out = torch.empty((P, thr.numel()), dtype=torch.float64, device=dev)
         poff_d, ngt_d = _i32(poff, dev), _i32(list(num_ground_truth), dev)
         lib = _lib.load()
+        nscratch = int(lib.yh_average_precision_scratch_bytes(P, dmax))   # 0 up to 8192 detections
+        scratch = torch.empty(nscratch, dtype=torch.uint8, device=dev) if nscratch else None
         with torch.cuda.device(dev):
             _lib.check(lib.yh_average_precision(
                 match.ground_truth.data_ptr(), match.iou.data_ptr(), conf.data_ptr(), poff_d.data_ptr(),
                 ngt_d.data_ptr(), P, dmax, thr.data_ptr(), thr.numel(), self.integral_method.n_points,
-                out.data_ptr(), _stream(conf)))
+                out.data_ptr(), scratch.data_ptr() if nscratch else None, nscratch, _stream(conf)))
         return out
 
     def compute_by_detections(self, match: DetGtMatch, confidence: torch.Tensor, num_ground_truth: int,
