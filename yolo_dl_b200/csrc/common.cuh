@@ -102,6 +102,7 @@ struct LayerTab {
   float ah[YH_MAX_LAYERS][YH_MAX_ANCHORS];  // anchors cast to f32 (detect_2d.rs:203-209)
   float aw[YH_MAX_LAYERS][YH_MAX_ANCHORS];
   const float* head[YH_MAX_LAYERS];    // [B, A*E, H, W]
+  int l2hint;                          // YH_L2_HINT: prefetch-size hint of the scattered logit loads
 };
 
 // Validates the layers and fills tab (host). heads may be NULL (then tab.head is NULL).
@@ -152,6 +153,19 @@ __device__ __forceinline__ float decode_center(float sig, int idx, float size) {
 __device__ __forceinline__ float decode_size(float sig, float anchor) {
   float t = sig * 2.0f;
   return (t * t) * anchor;
+}
+
+// One isolated 4-byte logit (class logits of an NMS candidate / a matched row: every element in
+// its own 128-byte line, 69 KB apart).  r1 measured 3.6 sectors of DRAM traffic per such request:
+// the L2 fills whole lines.  hint 1 asks for 64-byte fills (PTX .L2::64B prefetch size).
+__device__ __forceinline__ float ld_scatter(const float* p, const int hint) {
+  float v;
+  if (hint == 1) {
+    asm volatile("ld.global.nc.L2::64B.f32 %0, [%1];" : "=f"(v) : "l"(p));
+  } else {
+    v = __ldg(p);
+  }
+  return v;
 }
 
 // ---------------------------------------------------------------------------------

@@ -130,6 +130,11 @@ int build_layer_tab(const YhLayer* layers, int L, int C, const float* const* hea
     }
   }
   tab->N = (int)expect;
+  static const int l2hint = []() {
+    const char* e = getenv("YH_L2_HINT");
+    return e ? atoi(e) : 0;
+  }();
+  tab->l2hint = l2hint;
   return YH_OK;
 }
 

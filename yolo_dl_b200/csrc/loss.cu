@@ -577,7 +577,7 @@ loss_rows_kernel(const LayerTab t, const GradTab g, const LossParams p, const Ro
     if (own) {
       const float* hp = t.head[l] + off;
 #pragma unroll
-      for (int e = 0; e < 5; ++e) xb[e] = hp[(size_t)e * es];
+      for (int e = 0; e < 5; ++e) xb[e] = ld_scatter(hp + (size_t)e * es, t.l2hint);
     }
     float xc[kRowsPerWarp][kClsRegs];
 #pragma unroll
@@ -589,7 +589,7 @@ loss_rows_kernel(const LayerTab t, const GradTab g, const LossParams p, const Ro
 #pragma unroll
       for (int j = 0; j < kClsRegs; ++j) {
         const int k = lane + 32 * j;
-        xc[r][j] = (m0 + r < m_end && k < t.C) ? hp[(size_t)(5 + k) * es_r] : 0.0f;
+        xc[r][j] = (m0 + r < m_end && k < t.C) ? ld_scatter(hp + (size_t)(5 + k) * es_r, t.l2hint) : 0.0f;
       }
     }
 

@@ -169,7 +169,7 @@ nms_filter_kernel(const LayerTab t, const float thr, unsigned long long* __restr
 #pragma unroll
       for (int r = 0; r < kFilterClsRegs; ++r) {
         const int k = r * 32 + lane;
-        xc[r] = (k < t.C) ? __ldg(hp_s + (size_t)(5 + k) * es_s) : 0.0f;
+        xc[r] = (k < t.C) ? ld_scatter(hp_s + (size_t)(5 + k) * es_s, t.l2hint) : 0.0f;
       }
       for (int k0 = 0, r = 0; k0 < t.C; k0 += 32, ++r) {
         const int k = k0 + lane;
