@@ -125,6 +125,11 @@ __global__ void __launch_bounds__(kDenseThreads)
 loss_dense_kernel(const LayerTab t, const GradTab g, const int B, const float numel,
                   const float w_obj, const int reduction, const int kind, const float gamma,
                   double* __restrict__ partials, const int n_obj, const DenseTab d) {
+  // PDL: this kernel reads nothing an earlier kernel of its stream wrote, so it works first and
+  // waits for its predecessor only before it EXITS (completion stays transitive along the
+  // stream).  Consecutive ranged launches (yh_loss_dense_range per image group) then overlap the
+  // drain of one with the ramp-up of the next instead of losing ~1.5 us of bandwidth per launch.
+  griddep_launch();
   double acc = 0.0;
   if (GRAD) {
     // NOT a persistent kernel: the first n_obj CTAs do pass 1, every later CTA writes exactly one
@@ -166,6 +171,7 @@ loss_dense_kernel(const LayerTab t, const GradTab g, const int B, const float nu
         float4* q = reinterpret_cast<float4*>(gbase) + threadIdx.x;
 #pragma unroll
         for (int u = 0; u < kTileUnroll; ++u) st_stream4(q + u * kDenseThreads, zero4);
+        griddep_wait();
         return;
       }
       // a tile that meets an objectness plane or the end of the tensor: per-quad test, quads
@@ -192,6 +198,7 @@ loss_dense_kernel(const LayerTab t, const GradTab g, const int B, const float nu
             if (idx + k < len) st_stream1(gp + k, 0.0f);
         }
       }
+      griddep_wait();
       return;
     }
     // ---- pass 1: the quads that hold at least one objectness element ---------------------
@@ -294,6 +301,7 @@ loss_dense_kernel(const LayerTab t, const GradTab g, const int B, const float nu
     for (int k = 0; k < kDenseThreads / 32; ++k) tot += s_part[k];
     partials[(size_t)blockIdx.x * 4] = tot;
   }
+  griddep_wait();
 }
 
 // ---------------------------------------------------------------------------------
@@ -1081,9 +1089,10 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
     const bool bce = p.obj_kind == YH_LOSS_BCE;
     double* part = ws->partials + (size_t)part_off * 4;
     YH_TIME(YH_K_LOSS_DENSE, s);
-#define YH_DENSE(G, K)                                                                       \
-  loss_dense_kernel<G, K><<<(unsigned)(dense_grid + (G ? dense_tiles : 0)), kDenseThreads, 0, s>>>( \
-      dt_tab, dg, Bd, numel, p.w_obj, p.reduction, p.obj_kind, p.gamma, part, dense_grid, dt)
+#define YH_DENSE(G, K)                                                                          \
+  YH_CUDA(launch_pdl(loss_dense_kernel<G, K>, dim3((unsigned)(dense_grid + (G ? dense_tiles : 0))), \
+                     dim3(kDenseThreads), 0, s, dt_tab, dg, Bd, numel, p.w_obj, p.reduction,      \
+                     p.obj_kind, p.gamma, part, dense_grid, dt))
     if (grad_heads) {
       if (bce) YH_DENSE(true, true); else YH_DENSE(true, false);
     } else {
