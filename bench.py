@@ -491,6 +491,7 @@ def run_native(args):
     barrier()
     with ClockSampler(local) as clk:
         win_ms = time_windows(one_step, K, nwin, barrier, world, dev)
+    step.counts()   # raises if any replay of the timed region overflowed a buffer (sticky flag)
     replays = W + K * nwin
     launches = step.kernels_in_graph * K
     ms = statistics.median(win_ms)

@@ -362,6 +362,14 @@ int yh_read_counts(YhWorkspace* ws, const int32_t* M_dev, int32_t* M_host,
  * nonzero(), paid only when a batch outgrows the workspace.  Host value, no synchronisation. */
 int yh_workspace_candidates_needed(const YhWorkspace* ws);
 
+/* Device pointer to the workspace's sticky int32 overflow / order flag (bits: 1 matches, 2 NMS
+ * candidates, 4 NMS outputs, 8 unsorted match list; cleared by yh_read_counts).  A caller that
+ * replays a captured step and copies its results out asynchronously copies this word with them
+ * instead of paying yh_read_counts' synchronisation: non-zero = the step's outputs are truncated. */
+const int32_t* yh_workspace_error_flag(const YhWorkspace* ws);
+/* The same word copied to pinned host memory on `stream` (asynchronous, does not clear it). */
+int yh_copy_error_flag_async(YhWorkspace* ws, int32_t* flag_host_pinned, void* stream);
+
 /* Number of kernels this library has launched on the calling thread since the last
  * reset (bench.py's `gpu_launches`). */
 int64_t yh_launch_count(int reset);

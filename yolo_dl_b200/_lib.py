@@ -102,6 +102,8 @@ SYMBOLS = {
     "yh_read_counts": (c_int, [c_void_p, c_void_p, POINTER(c_int32), c_void_p, POINTER(c_int32),
                                c_void_p]),
     "yh_workspace_candidates_needed": (c_int, [c_void_p]),
+    "yh_workspace_error_flag": (c_void_p, [c_void_p]),
+    "yh_copy_error_flag_async": (c_int, [c_void_p, c_void_p, c_void_p]),
     "yh_launch_count": (c_int64, [c_int]),
     "yh_timing_enable": (c_int, [c_int]),
     "yh_trace_enable": (c_int, [c_void_p, c_int]),

@@ -331,6 +331,16 @@ int yh_workspace_create(int device, int max_batch, int64_t max_instances, int ca
   return YH_OK;
 }
 
+const int32_t* yh_workspace_error_flag(const YhWorkspace* ws) { return ws ? ws->err_flag : nullptr; }
+
+int yh_copy_error_flag_async(YhWorkspace* ws, int32_t* flag_host_pinned, void* stream) {
+  YH_REQUIRE(ws != nullptr && flag_host_pinned != nullptr, "NULL argument");
+  YH_CUDA(cudaSetDevice(ws->device));
+  YH_CUDA(cudaMemcpyAsync(flag_host_pinned, ws->err_flag, sizeof(int32_t), cudaMemcpyDeviceToHost,
+                          (cudaStream_t)stream));
+  return YH_OK;
+}
+
 int yh_workspace_candidates_needed(const YhWorkspace* ws) {
   return ws ? ws->cand_need_host : 0;
 }

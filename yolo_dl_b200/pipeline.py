@@ -349,6 +349,15 @@ class DeviceStep:
         return self.ws.read_counts(torch.cuda.current_stream(self.dev).cuda_stream, self.M, self.K)
 
 
+def _check_flag(h_counts, what):
+    f = int(h_counts[2])
+    if f:
+        raise _lib.YoloHotError(
+            _lib.YH_ERR_INVALID if f & 8 else _lib.YH_ERR_CAPACITY,
+            f"{what}: the step's sticky flag is {f} (1=matches, 2=nms candidates, 4=nms outputs overflowed; "
+            "8=match list not sorted): outputs are truncated — enlarge the capacities")
+
+
 class HostStep:
     """The step for HOST-resident inputs and outputs.  Per call: H2D of the L head tensors and
     the packed labels from pinned memory, DeviceStep, D2H of [losses4, M, K], the match list, the
@@ -361,7 +370,10 @@ class HostStep:
                         for l in range(st.L)]
         pin = dict(pin_memory=True)
         self.h_losses = torch.empty(4, dtype=torch.float32, **pin)
-        self.h_counts = torch.empty(2, dtype=torch.int32, **pin)
+        self.h_counts = torch.empty(3, dtype=torch.int32, **pin)   # M, K, sticky overflow flag
+        self.h_counts.zero_()
+        # the workspace's sticky flag travels out with the results (yh_copy_error_flag_async in
+        # copy_out): a replayed step must not truncate matches / candidates / detections silently
         self.h_match = torch.empty((2, st.mcap), dtype=torch.int64, **pin)
         self.h_det = torch.empty((3, st.kcap), dtype=torch.int64, **pin)
         self.h_tlbr = torch.empty((st.kcap, 4), dtype=torch.float32, **pin)
@@ -381,6 +393,8 @@ class HostStep:
         self.h_losses.copy_(st.losses4, non_blocking=True)
         self.h_counts[0:1].copy_(st.M, non_blocking=True)
         self.h_counts[1:2].copy_(st.K, non_blocking=True)
+        _lib.check(st.lib.yh_copy_error_flag_async(st.ws.handle, self.h_counts[2:3].data_ptr(),
+                                                   torch.cuda.current_stream(st.dev).cuda_stream))
         self.h_match[0].copy_(st.m_batch, non_blocking=True)
         self.h_match[1].copy_(st.m_flat, non_blocking=True)
         self.h_det[0].copy_(st.kb, non_blocking=True)
@@ -388,7 +402,7 @@ class HostStep:
         self.h_det[2].copy_(st.ki, non_blocking=True)
         self.h_tlbr.copy_(st.tlbr, non_blocking=True)
         self.h_conf.copy_(st.conf, non_blocking=True)
-        d2h = 16 + 8 + self.h_match.numel() * 8 + self.h_det.numel() * 8 + self.h_tlbr.numel() * 4 \
+        d2h = 16 + 12 + self.h_match.numel() * 8 + self.h_det.numel() * 8 + self.h_tlbr.numel() * 4 \
             + self.h_conf.numel() * 4
         if self.h_grads is not None:
             for h, d in zip(self.h_grads, st.grads):
@@ -415,6 +429,7 @@ class HostStep:
         d2h = self.copy_out()
         torch.cuda.current_stream(st.dev).synchronize()
         self.h2d_bytes, self.d2h_bytes = h2d, d2h
+        _check_flag(self.h_counts, "HostStep.run")
         return self.h_losses, int(self.h_counts[0]), int(self.h_counts[1])
 
 
@@ -492,6 +507,7 @@ class HostPipeline:
     def result(self, k):
         self.ev_out[k].synchronize()
         hs = self.slots[k]
+        _check_flag(hs.h_counts, "HostPipeline.result")
         return hs.h_losses, int(hs.h_counts[0]), int(hs.h_counts[1])
 
     def drain(self):
