@@ -52,7 +52,7 @@ def launches(path, out):
                 f.write(f"- {k}: {len(v)} launches, mean {sum(v) / len(v) / 1e3:.2f} us\n")
 
 
-def full(rep, out_csv, traffic_path):
+def full(rep, out_csv, traffic_path, tag, command, commit):
     raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(raw.splitlines()))
     hdr, units = rows[0], rows[1]
@@ -78,6 +78,11 @@ def full(rep, out_csv, traffic_path):
             per[short(r[hdr.index("Kernel Name")])].append(val("dram__bytes_read.sum") + val("dram__bytes_write.sum"))
     for k, v in per.items():
         traffic[k] = sum(v) / len(v)
+    # provenance: bench.py prints it as roofline.traffic_source, so that the DRAM-byte figure of
+    # the bench line can be traced to the capture (and the source state) it came from
+    traffic["_source"] = {"capture": f"profiles/{tag}_ncu_full.csv", "commit": commit, "command": command,
+                          "what": "dram__bytes_read.sum + dram__bytes_write.sum per launch, mean over the "
+                                  "captured launches of each kernel"}
     json.dump(traffic, open(traffic_path, "w"), indent=1, sort_keys=True)
 
 
@@ -86,10 +91,16 @@ if __name__ == "__main__":
     ap.add_argument("tag")
     ap.add_argument("--launches")
     ap.add_argument("--rep")
+    ap.add_argument("--command", default="ncu --set full --clock-control none --import-source on -k regex:<kernels> "
+                                         "python bench.py --steps 3 --warmup 3 --no-e2e --no-cpu-baseline --no-extras")
+    ap.add_argument("--commit", default=None)
     a = ap.parse_args()
+    if a.commit is None:
+        a.commit = subprocess.run(["git", "-C", ROOT, "rev-parse", "--short", "HEAD"], capture_output=True,
+                                  text=True).stdout.strip()
     os.makedirs(os.path.join(ROOT, "profiles"), exist_ok=True)
     if a.launches:
         launches(a.launches, os.path.join(ROOT, "profiles", f"{a.tag}_launches.md"))
     if a.rep:
         full(a.rep, os.path.join(ROOT, "profiles", f"{a.tag}_ncu_full.csv"),
-             os.path.join(ROOT, "profiles", "traffic.json"))
+             os.path.join(ROOT, "profiles", "traffic.json"), a.tag, a.command, a.commit)
