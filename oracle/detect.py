@@ -35,11 +35,18 @@ def make_infos(shapes: Sequence[Tuple[int, int]], anchors) -> List[LayerInfo]:
     return infos
 
 
-def detect2d_forward(head: torch.Tensor, num_classes: int, anchors):
+def detect2d_forward(head: torch.Tensor, num_classes: int, anchors, divisor_as_tensor: bool = False):
     """Detect2D::forward (tch-modules/src/detect_2d.rs:42-152), cache (:196-221).
 
     head: [B, A*(5+C), H, W] f32.  Returns dict of cy,cx,h,w [B,1,A,H,W] and the
     obj_logit / class_logit VIEWS of the input.
+
+    `tensor / f64 scalar` is what the reference writes (:69-70,:128-131).  ATen evaluates it as an
+    IEEE division on the CPU but as a multiplication by the f32 reciprocal on CUDA
+    (BinaryDivTrueKernel.cu, "may lose one bit of precision"), so the reference's own CPU and CUDA
+    results differ in the last bit of cy / cx.  `divisor_as_tensor` divides by a 0-dim tensor ON THE
+    DEVICE instead, which takes ATen's true-division kernel on either device: the CUDA executor
+    then follows the CPU's (and this library's) arithmetic bit for bit.
     """
     B, ch, H, W = head.shape
     A = len(anchors)
@@ -53,8 +60,14 @@ def detect2d_forward(head: torch.Tensor, num_classes: int, anchors):
     anchor_h, anchor_w = anchor_h.to(head.device), anchor_w.to(head.device)
 
     outputs = head.view(B, E, A, H, W)  # (:66)
-    cy = (outputs[:, 0:1].sigmoid() * 2.0 - 0.5) / float(H) + y_offsets.view(1, 1, 1, H, 1)
-    cx = (outputs[:, 1:2].sigmoid() * 2.0 - 0.5) / float(W) + x_offsets.view(1, 1, 1, 1, W)
+    dh, dw = float(H), float(W)
+    if divisor_as_tensor:
+        dh = torch.tensor(float(H), dtype=torch.float32, device=head.device)
+        dw = torch.tensor(float(W), dtype=torch.float32, device=head.device)
+        y_offsets = torch.arange(H, dtype=torch.float32, device=head.device) / dh
+        x_offsets = torch.arange(W, dtype=torch.float32, device=head.device) / dw
+    cy = (outputs[:, 0:1].sigmoid() * 2.0 - 0.5) / dh + y_offsets.view(1, 1, 1, H, 1)
+    cx = (outputs[:, 1:2].sigmoid() * 2.0 - 0.5) / dw + x_offsets.view(1, 1, 1, 1, W)
     h = outputs[:, 2:3].sigmoid().mul(2.0).pow(2) * anchor_h.view(1, 1, A, 1, 1)
     w = outputs[:, 3:4].sigmoid().mul(2.0).pow(2) * anchor_w.view(1, 1, A, 1, 1)
     obj_logit = outputs[:, 4:5]
@@ -72,8 +85,9 @@ def merge(dets: Sequence[dict], num_classes: int):
     return out
 
 
-def forward_merged(heads: Sequence[torch.Tensor], infos: Sequence[LayerInfo], num_classes: int):
-    dets = [detect2d_forward(h, num_classes, i.anchors) for h, i in zip(heads, infos)]
+def forward_merged(heads: Sequence[torch.Tensor], infos: Sequence[LayerInfo], num_classes: int,
+                   divisor_as_tensor: bool = False):
+    dets = [detect2d_forward(h, num_classes, i.anchors, divisor_as_tensor) for h, i in zip(heads, infos)]
     return merge(dets, num_classes)
 
 
