@@ -236,6 +236,26 @@ __device__ __forceinline__ void smem_passes(unsigned long long* s, const int n, 
 __device__ void sort_keys(unsigned long long* __restrict__ keys, const int K,
                           unsigned long long* s) {
   if (K <= 1) return;
+  if (K <= kNmsThreads) {
+    // rank sort: keys are unique (the index is part of the key), so the sorted position of a key
+    // is the number of smaller keys — K broadcast reads of shared memory per thread and two
+    // barriers, where the bitonic network below needs log2(P)*(log2(P)+1)/2 block-wide passes
+    // (36 for the ~200 candidates per image of a training step: ~5 us of barriers on one SM)
+    unsigned long long my = 0;
+    if ((int)threadIdx.x < K) {
+      my = keys[threadIdx.x];
+      s[threadIdx.x] = my;
+    }
+    __syncthreads();
+    if ((int)threadIdx.x < K) {
+      int rank = 0;
+#pragma unroll 8
+      for (int i = 0; i < K; ++i) rank += s[i] < my;
+      keys[rank] = my;
+    }
+    __syncthreads();
+    return;
+  }
   int P = 2;
   while (P < K) P <<= 1;
   if (P <= kSortTile) {
