@@ -308,6 +308,7 @@ extern "C" int yh_assign(YhWorkspace* ws, const double* gt_dev, const int32_t* g
   }
   cudaStream_t s = (cudaStream_t)stream;
   YH_CUDA(cudaSetDevice(ws->device));
+  note_batch(B);
   YH_TIME(YH_K_ASSIGN_SLOTS, s);
   const int words = (t.N + 31) / 32;
   assign_slots_kernel<<<B, kAssignThreads, 0, s>>>(t, gt_dev, gt_offsets_dev, ws->slot_dist,

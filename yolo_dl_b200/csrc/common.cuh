@@ -71,7 +71,8 @@ void timing_end(cudaStream_t s);
 __device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
-bool pdl_enabled();  // YH_PDL=0 turns the attribute off (A/B)
+bool pdl_enabled();   // YH_PDL=0/1 forces; default: on for calls on batches of <= 16 images
+void note_batch(int B);  // the entry points tell the batch size of the call on this thread
 
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem,
@@ -229,6 +230,7 @@ struct YhWorkspace {
   long long* big_grp;             // [8 groups * big_len]
   long long big_len;              // = cand_stride
   unsigned* big_sync;             // barrier counters | cross-test masks | kept counts (YH_BIG_SYNC_WORDS)
+  unsigned* big_mat;              // [8 groups][2][2][512 * 16] suppression bit matrices of the tiles in flight
   int* cand_need;                 // device: largest candidate count that exceeded the capacity
   int cand_need_host;             // its value at the last yh_read_counts
 

@@ -212,13 +212,14 @@ ap_kernel(const int* __restrict__ det_gt, const double* __restrict__ det_iou,
   }
   int P = 2;
   while (P < D) P <<= 1;
-  // the scan partials always live in shared memory; the four per-detection arrays too when the
-  // problem fits (<= kApMax detections), else in this problem's slice of the caller's scratch
+  // the scan partials always live in shared memory; the four per-detection arrays too when every
+  // problem of the launch fits (<= kApMax detections), else in this problem's slice of the caller's scratch
   // (L2-resident; the same code walks either through generic pointers)
   double* s_dpart = reinterpret_cast<double*>(smem_raw);  // kApThreads doubles (also the point values)
   int* s_ipart = reinterpret_cast<int*>(s_dpart + kApThreads);  // kApThreads ints
-  unsigned char* arrays = (P <= kApMax) ? reinterpret_cast<unsigned char*>(s_ipart + kApThreads)
-                                        : scratch + (size_t)p * scratch_per_problem;
+  // (one decision per LAUNCH: with scratch the shared-memory request holds the partials only)
+  unsigned char* arrays = (scratch == nullptr) ? reinterpret_cast<unsigned char*>(s_ipart + kApThreads)
+                                               : scratch + (size_t)p * scratch_per_problem;
   double* env = reinterpret_cast<double*>(arrays);
   int* idx = reinterpret_cast<int*>(env + P);
   int* tp = idx + P;
@@ -377,7 +378,8 @@ int yh_average_precision(const int32_t* det_gt_dev, const double* det_iou_dev,
   ap_kernel<<<num_problems, kApThreads, smem, s>>>(det_gt_dev, det_iou_dev, det_conf_dev,
                                                    problem_offsets_dev, num_ground_truth_dev,
                                                    iou_thresholds_dev, num_thresholds, n_points,
-                                                   out_ap_dev, (unsigned char*)scratch_dev,
+                                                   out_ap_dev,
+                                                   need ? (unsigned char*)scratch_dev : nullptr,
                                                    need ? ap_array_bytes(P) : (size_t)0);
   YH_LAUNCHED(s);
   return YH_OK;

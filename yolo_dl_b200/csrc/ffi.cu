@@ -21,12 +21,19 @@ void set_error(const char* fmt, ...) {
 
 int64_t& launch_counter() { return g_launches; }
 
+// PDL pays where the step is launch-latency-bound (8 images per GPU: 53.7 -> 50.4 us, r2) and
+// costs where it is bandwidth-bound (64 images: 178 -> 189 us — early-launched dependents sit on
+// SM resources the streaming kernels want), so by default it follows the batch size of the call.
+static thread_local int g_pdl_batch = 1;
+void note_batch(int B) { g_pdl_batch = B; }
+
 bool pdl_enabled() {
-  static const bool on = []() {
+  static const int forced = []() {
     const char* e = getenv("YH_PDL");
-    return !(e && e[0] == '0');
+    return e ? (e[0] == '0' ? 0 : 1) : -1;
   }();
-  return on;
+  if (forced >= 0) return forced != 0;
+  return g_pdl_batch <= 16;
 }
 
 // ---- optional per-launch timing: one CUDA event pair per launch, on the launch stream ----
@@ -234,6 +241,7 @@ int yh_workspace_destroy(YhWorkspace* ws) {
   cudaFree(ws->big_box);
   cudaFree(ws->big_grp);
   cudaFree(ws->big_sync);
+  cudaFree(ws->big_mat);
   cudaFree(ws->cand_need);
   cudaFree(ws->err_flag);
   if (ws->host_counts) cudaFreeHost(ws->host_counts);
@@ -310,6 +318,7 @@ int yh_workspace_create(int device, int max_batch, int64_t max_instances, int ca
     YH_ALLOC(ws->big_box, (size_t)8 * (size_t)ws->big_len * sizeof(float4));
     YH_ALLOC(ws->big_grp, (size_t)8 * (size_t)ws->big_len * sizeof(long long));
     YH_ALLOC(ws->big_sync, YH_BIG_SYNC_WORDS * sizeof(unsigned));
+    YH_ALLOC(ws->big_mat, (size_t)8 * 2 * 2 * 512 * 16 * sizeof(unsigned));
   }
   YH_ALLOC(ws->err_flag, 64);
 #undef YH_ALLOC

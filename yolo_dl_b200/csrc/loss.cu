@@ -1035,6 +1035,7 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
 
   cudaStream_t s = (cudaStream_t)stream;
   YH_CUDA(cudaSetDevice(ws->device));
+  note_batch(B);
   const float numel = (float)((long long)B * tab.N);
   // objectness CTAs (and the whole grid of the forward-only form) per SM.  Sweep on B200
   // (profiles/README.md, r1f): 1 -> 78.4 us, 2 -> 77.1, 3 -> 77.9, 4 -> 79.1, 8 -> 80.6; tiles of

@@ -334,6 +334,42 @@ constexpr int kTileWords = kTile / 32;
 constexpr size_t kSegSmem = (size_t)kSortTile * sizeof(unsigned long long) +
                             (size_t)kTile * kTileWords * sizeof(unsigned);
 
+// In-order walk of one tile by ONE warp.  rem: lane w holds word w of the removed set (bit set =
+// not a survivor); mask: the tile's suppression bits in shared memory, row r at
+// mask[r*kTileWords + word], upper triangle.  Per 32-candidate word the 32 in-word rows are read
+// into registers (broadcast loads), the word is resolved by a 32-step chain of pure ALU
+// operations, and the rows of what it kept are OR-ed into the later words with independent loads
+// (lane = word): ~300 cycles per word whatever is kept, where the first version paid a dependent
+// shared-memory load plus a shuffle (~120 cycles) per KEPT box — 30 us for a tile of survivors.
+// Returns the keep bits, lane w holding word w.
+__device__ __forceinline__ unsigned walk_tile(const unsigned* mask, unsigned rem, const int nwords,
+                                              const int lane) {
+  unsigned keep = 0u;
+  for (int w = 0; w < nwords; ++w) {
+    unsigned cur = __shfl_sync(0xffffffffu, rem, w);
+    unsigned m[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) m[j] = mask[(w * 32 + j) * kTileWords + w];
+    unsigned kw = 0u;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      const bool k = !((cur >> j) & 1u);
+      kw |= k ? (1u << j) : 0u;
+      cur |= k ? m[j] : 0u;  // rows of suppressed candidates may hold anything: never used
+    }
+    unsigned add = 0u, t = kw;
+    const bool later = lane > w && lane < nwords;
+    while (t) {
+      const int j = __ffs(t) - 1;
+      t &= t - 1;
+      if (later) add |= mask[(w * 32 + j) * kTileWords + lane];
+    }
+    rem |= add;
+    if (lane == w) keep = kw;
+  }
+  return keep;
+}
+
 template <class P>
 __global__ void __launch_bounds__(kNmsThreads)
 nms_segment_kernel(const P prov, const SegView v, const double iou_thr) {
@@ -431,22 +467,8 @@ nms_segment_kernel(const P prov, const SegView v, const double iou_thr) {
 
     // ---- c. in-order walk, one warp ----------------------------------------------------------
     if (wid == 0) {
-      unsigned rem = (lane < nwords) ? ~(s_al[0][lane] & s_al[1][lane]) : ~0u;
-      unsigned keep = 0u;
-      for (int w = 0; w < nwords; ++w) {
-        unsigned cur = __shfl_sync(0xffffffffu, rem, w);
-        unsigned kw = 0u;
-        while (~cur) {
-          const int j = __ffs(~cur) - 1;
-          kw |= 1u << j;
-          const int r = w * 32 + j;
-          const unsigned mrow = (lane >= w && lane < nwords) ? mask[r * kTileWords + lane] : 0u;
-          rem |= mrow;
-          cur |= __shfl_sync(0xffffffffu, mrow, w) | ((2u << j) - 1u);
-        }
-        if (lane == w) keep = kw;
-      }
-      s_keep[lane] = keep;
+      const unsigned rem = (lane < nwords) ? ~(s_al[0][lane] & s_al[1][lane]) : ~0u;
+      s_keep[lane] = walk_tile(mask, rem, nwords, lane);
     }
     __syncthreads();
 
@@ -501,7 +523,7 @@ nms_segment_kernel(const P prov, const SegView v, const double iou_thr) {
 constexpr int kBigThreads = 1024;
 constexpr int kBigMin = YH_BIG_MIN;
 constexpr int kBigGroups = 8;
-constexpr int kStage = 2048;  // kept boxes a tester CTA stages in shared memory per round (48 KB)
+constexpr int kStage = 1024;  // kept boxes a tester CTA stages in shared memory per round (24 KB)
 
 struct BigView {
   float4* box;        // [kBigGroups * len] boxes of the segment a group is working on, sorted order
@@ -510,6 +532,7 @@ struct BigView {
   unsigned* sync;     // [kBigGroups * 32] barrier counters, zero at launch
   unsigned* dead;     // [kBigGroups * 2 * kTileWords] cross-test masks, zero at launch
   int* nkept;         // [kBigGroups * 2] kept count as of the start of a phase (double-buffered)
+  unsigned* mat;      // [kBigGroups][2 parities][in-tile | previous-tile][kTile * kTileWords] bit matrices
 };
 
 // barrier of the n CTAs of a group: a monotonically increasing arrival counter
@@ -680,13 +703,12 @@ nms_big_kernel(const P prov, const SegView v, const int S, const BigView big,
       const int ntiles = (K + kTile - 1) / kTile;
       const int ti = threadIdx.x & (kTile - 1);
       const int half = threadIdx.x >> 9;
-      unsigned* mask = reinterpret_cast<unsigned*>(s_keys);                  // 32 KB
-      float4* p_box = reinterpret_cast<float4*>(mask + kTile * kTileWords);  // 8 KB: previous tile's kept
-      long long* p_grp = reinterpret_cast<long long*>(p_box + kTile);        // 4 KB
-      int nkept = 0, npk = 0;
-      for (int p = 0; p < ntiles; ++p) {
-        if (r == 0 || csz == 1) {
-          // resolver: tile p
+      unsigned* mask = reinterpret_cast<unsigned*>(s_keys);  // resolver: 32 KB in-tile bit matrix
+      int nkept = 0;
+      if (csz == 1) {
+        // a group of one CTA (a GPU with fewer than two SMs per group): everything on this CTA,
+        // unpipelined — the same passes as nms_segment_kernel, kept list read from global memory
+        for (int p = 0; p < ntiles; ++p) {
           const int base = p * kTile;
           const int nt = min(K - base, kTile);
           const int nwords = (nt + 31) >> 5;
@@ -699,21 +721,10 @@ nms_big_kernel(const P prov, const SegView v, const int S, const BigView big,
             box = __ldcg(bbox + base + ti);
             grp = __ldcg(bgrp + base + ti);
             const float area = box_area(box);
-            if (csz > 1) {
-              unsigned dw;
-              asm volatile("ld.relaxed.gpu.u32 %0, [%1];" : "=r"(dw) : "l"(dead + (p & 1) * kTileWords + (ti >> 5)) : "memory");
-              alive = !((dw >> (ti & 31)) & 1u);
-              // boxes kept by tile p-1 (the testers of phase p-1 could not know them)
-              for (int q = half; alive && q < npk; q += 2)
-                if (p_grp[q] == grp && suppresses(p_box[q], box_area(p_box[q]), box, area, iou_thr))
-                  alive = false;
-            } else {
-              // a group of one CTA: the whole kept list, unpipelined
-              for (int q = half; alive && q < nkept; q += 2) {
-                const float4 kb = __ldcg(kept_box + q);
-                if (__ldcg(kept_grp + q) == grp && suppresses(kb, box_area(kb), box, area, iou_thr))
-                  alive = false;
-              }
+            for (int q = half; alive && q < nkept; q += 2) {
+              const float4 kb = __ldcg(kept_box + q);
+              if (__ldcg(kept_grp + q) == grp && suppresses(kb, box_area(kb), box, area, iou_thr))
+                alive = false;
             }
           }
           if (half == 0) {
@@ -725,17 +736,12 @@ nms_big_kernel(const P prov, const SegView v, const int S, const BigView big,
             if (lane == 0) s_al[half][wid & (kTileWords - 1)] = am;
           }
           __syncthreads();
-          if (csz > 1 && threadIdx.x < kTileWords) dead[(p & 1) * kTileWords + threadIdx.x] = 0u;
-          // suppression bits among the survivors (upper triangle)
           for (int item = wid; item < nt * nwords; item += kBigThreads / 32) {
             const int rr = item / nwords, w = item - rr * nwords;
             if (w < (rr >> 5)) continue;
-            const unsigned al_r = s_al[0][rr >> 5] & s_al[1][rr >> 5];
-            if (!((al_r >> (rr & 31)) & 1u)) continue;
             const int j = w * 32 + lane;
-            const unsigned al_w = s_al[0][w] & s_al[1][w];
             bool hit = false;
-            if (j > rr && ((al_w >> lane) & 1u)) {
+            if (j > rr && j < nt) {
               const float4 br = t_box[rr], bj = t_box[j];
               hit = t_grp[rr] == t_grp[j] && suppresses(br, box_area(br), bj, box_area(bj), iou_thr);
             }
@@ -744,22 +750,8 @@ nms_big_kernel(const P prov, const SegView v, const int S, const BigView big,
           }
           __syncthreads();
           if (wid == 0) {
-            unsigned rem = (lane < nwords) ? ~(s_al[0][lane] & s_al[1][lane]) : ~0u;
-            unsigned keep = 0u;
-            for (int w = 0; w < nwords; ++w) {
-              unsigned cur = __shfl_sync(0xffffffffu, rem, w);
-              unsigned kw = 0u;
-              while (~cur) {
-                const int j = __ffs(~cur) - 1;
-                kw |= 1u << j;
-                const int rr = w * 32 + j;
-                const unsigned mrow = (lane >= w && lane < nwords) ? mask[rr * kTileWords + lane] : 0u;
-                rem |= mrow;
-                cur |= __shfl_sync(0xffffffffu, mrow, w) | ((2u << j) - 1u);
-              }
-              if (lane == w) keep = kw;
-            }
-            s_keep[lane] = keep;
+            const unsigned rem = (lane < nwords) ? ~(s_al[0][lane] & s_al[1][lane]) : ~0u;
+            s_keep[lane] = walk_tile(mask, rem, nwords, lane);
           }
           __syncthreads();
           int before_k = 0, total_k = 0;
@@ -771,60 +763,188 @@ nms_big_kernel(const P prov, const SegView v, const int S, const BigView big,
           }
           const unsigned kwm = s_keep[ti >> 5];
           if (half == 0 && ((kwm >> (ti & 31)) & 1u)) {
-            const int lp = before_k + __popc(kwm & ((1u << (ti & 31)) - 1u));
-            kept_key[nkept + lp] = key;
-            kept_box[nkept + lp] = box;
-            kept_grp[nkept + lp] = grp;
-            p_box[lp] = box;
-            p_grp[lp] = grp;
+            const int lp = nkept + before_k + __popc(kwm & ((1u << (ti & 31)) - 1u));
+            kept_key[lp] = key;
+            kept_box[lp] = box;
+            kept_grp[lp] = grp;
           }
           nkept += total_k;
-          npk = total_k;
-          // what the testers of phase p+1 work against: everything kept by tiles <= p
-          if (threadIdx.x == 0) nk_pub[(p + 1) & 1] = nkept;
-        } else if (p + 1 < ntiles) {
-          // tester: tile p+1 against the boxes kept by tiles < p
-          int n0;
-          asm volatile("ld.relaxed.gpu.s32 %0, [%1];" : "=r"(n0) : "l"(nk_pub + (p & 1)) : "memory");
-          const int T = csz - 1, tr = r - 1;
-          const int lo = (int)((long long)n0 * tr / T), hi = (int)((long long)n0 * (tr + 1) / T);
-          const int base = (p + 1) * kTile;
-          const int nt = min(K - base, kTile);
-          bool hit = false;
-          float4 box = make_float4(0.f, 0.f, 0.f, 0.f);
-          long long grp = 0;
-          if (ti < nt && lo < hi) {
-            box = __ldcg(bbox + base + ti);
-            grp = __ldcg(bgrp + base + ti);
-          }
-          const float area = box_area(box);
-          // my share of the kept list goes through shared memory (L2 -> smem once per CTA, then
-          // broadcast reads); __ldcg: other CTAs wrote these lines during this kernel
-          float4* st_box = reinterpret_cast<float4*>(s_keys);                 // kStage x 16 B
-          long long* st_grp = reinterpret_cast<long long*>(st_box + kStage);  // kStage x 8 B
-          for (int c0 = lo; c0 < hi; c0 += kStage) {
-            const int cnt = min(kStage, hi - c0);
-            for (int i = threadIdx.x; i < cnt; i += kBigThreads) {
-              st_box[i] = __ldcg(kept_box + c0 + i);
-              st_grp[i] = __ldcg(kept_grp + c0 + i);
-            }
-            __syncthreads();
-            if (ti < nt && !hit) {
-              for (int q = half; q < cnt; q += 2) {
-                const float4 kb = st_box[q];
-                if (st_grp[q] == grp && suppresses(kb, box_area(kb), box, area, iou_thr)) {
-                  hit = true;
-                  break;
+          __threadfence();  // the next tile reads the kept list through the L2
+          __syncthreads();
+        }
+      } else {
+        // Phase p (p = -1 .. ntiles-1), one group barrier each:
+        //   CTAs 1..  prepare tile p+1 — everything that is a pure function of the boxes plus the
+        //             test against the kept list as it stood before tile p:
+        //               dead    (512 bits)   box of tile p+1 suppressed by a box kept by tiles < p
+        //               m_in    (512 x 512)  in-tile suppression bits, upper triangle
+        //               m_prev  (512 x 512)  bit (i, j): candidate i of tile p suppresses j of tile p+1
+        //   CTA 0     resolves tile p from what phase p-1 prepared: alive = ~dead & ~OR of the
+        //             m_prev rows of the candidates tile p-1 KEPT, then the in-order walk over
+        //             m_in — no IoU arithmetic at all on the serial path.
+        unsigned* s_prev_keep = reinterpret_cast<unsigned*>(t_grp);  // resolver: keep words of tile p-1
+        unsigned* s_or = s_prev_keep + 32;                           // resolver: OR of m_prev rows
+        if (r == 0 && threadIdx.x < 32) s_prev_keep[threadIdx.x] = 0u;
+        for (int p = -1; p < ntiles; ++p) {
+          if (r == 0) {
+            if (p >= 0) {
+              const int base = p * kTile;
+              const int nt = min(K - base, kTile);
+              const int nwords = (nt + 31) >> 5;
+              const unsigned* m_in = big.mat + ((size_t)(g * 2 + (p & 1)) * 2 + 0) * (kTile * kTileWords);
+              const unsigned* m_prev = big.mat + ((size_t)(g * 2 + (p & 1)) * 2 + 1) * (kTile * kTileWords);
+              // the in-tile matrix into shared memory (32 KB, two 16-byte loads per thread)
+              {
+                const uint4* src4 = reinterpret_cast<const uint4*>(m_in);
+                uint4* dst4 = reinterpret_cast<uint4*>(mask);
+                const uint4 v0 = __ldcg(src4 + threadIdx.x), v1 = __ldcg(src4 + kBigThreads + threadIdx.x);
+                dst4[threadIdx.x] = v0;
+                dst4[kBigThreads + threadIdx.x] = v1;
+              }
+              // my candidate (threads 0..511) and its cross-test bit
+              bool alive = half == 0 && ti < nt;
+              unsigned long long key = 0;
+              float4 box = make_float4(0.f, 0.f, 0.f, 0.f);
+              long long grp = 0;
+              if (alive) {
+                key = __ldcg(keys + base + ti);
+                box = __ldcg(bbox + base + ti);
+                grp = __ldcg(bgrp + base + ti);
+                unsigned dw;
+                asm volatile("ld.relaxed.gpu.u32 %0, [%1];" : "=r"(dw) : "l"(dead + (p & 1) * kTileWords + (ti >> 5)) : "memory");
+                alive = !((dw >> (ti & 31)) & 1u);
+              }
+              // OR of the m_prev rows of what tile p-1 kept: a warp per 16 rows, lane = word
+              if (threadIdx.x < kTileWords) s_or[threadIdx.x] = 0u;
+              __syncthreads();
+              if (p > 0) {
+                unsigned acc = 0u;
+                const unsigned pk = s_prev_keep[wid >> 1];          // rows wid*16 .. wid*16+15
+                const unsigned bits = (pk >> ((wid & 1) * 16)) & 0xffffu;
+                if (lane < kTileWords) {
+                  unsigned t = bits;
+                  while (t) {
+                    const int j = __ffs(t) - 1;
+                    t &= t - 1;
+                    acc |= __ldcg(m_prev + (wid * 16 + j) * kTileWords + lane);
+                  }
+                  if (acc) atomicOr(&s_or[lane], acc);
                 }
               }
+              __syncthreads();
+              if (alive) alive = !((s_or[ti >> 5] >> (ti & 31)) & 1u);
+              if (half == 0) {
+                const unsigned am = __ballot_sync(0xffffffffu, alive);
+                if (lane == 0) s_al[0][wid] = am;
+              }
+              __syncthreads();
+              if (threadIdx.x < kTileWords) dead[(p & 1) * kTileWords + threadIdx.x] = 0u;
+              if (wid == 0) {
+                const unsigned rem = (lane < nwords) ? ~s_al[0][lane] : ~0u;
+                s_keep[lane] = walk_tile(mask, rem, nwords, lane);
+              }
+              __syncthreads();
+              int before_k = 0, total_k = 0;
+#pragma unroll
+              for (int w = 0; w < kTileWords; ++w) {
+                const int c = __popc(s_keep[w]);
+                if (w < (ti >> 5)) before_k += c;
+                total_k += c;
+              }
+              const unsigned kwm = s_keep[ti >> 5];
+              if (half == 0 && ((kwm >> (ti & 31)) & 1u)) {
+                const int lp = nkept + before_k + __popc(kwm & ((1u << (ti & 31)) - 1u));
+                kept_key[lp] = key;
+                kept_box[lp] = box;
+                kept_grp[lp] = grp;
+              }
+              nkept += total_k;
+              if (threadIdx.x < 32) s_prev_keep[threadIdx.x] = threadIdx.x < kTileWords ? s_keep[threadIdx.x] : 0u;
+              // what the testers of phase p+1 work against: everything kept by tiles <= p
+              if (threadIdx.x == 0) nk_pub[(p + 1) & 1] = nkept;
+            }
+          } else if (p + 1 < ntiles) {
+            const int q = p + 1;  // the tile this phase prepares
+            const int T = csz - 1, tr = r - 1;
+            const int base = q * kTile;
+            const int nt = min(K - base, kTile);
+            // boxes of tile q and of tile q-1 in shared memory
+            float4* q_box = reinterpret_cast<float4*>(s_keys);             // 8 KB
+            long long* q_grp = reinterpret_cast<long long*>(q_box + kTile);  // 4 KB
+            float4* o_box = reinterpret_cast<float4*>(q_grp + kTile);       // 8 KB (tile q-1)
+            long long* o_grp = reinterpret_cast<long long*>(o_box + kTile);  // 4 KB
+            float4* st_box = reinterpret_cast<float4*>(o_grp + kTile);      // kStage x 16 B
+            long long* st_grp = reinterpret_cast<long long*>(st_box + kStage);
+            if (half == 0) {
+              const bool in = ti < nt;
+              q_box[ti] = in ? __ldcg(bbox + base + ti) : make_float4(0.f, 0.f, 0.f, 0.f);
+              q_grp[ti] = in ? __ldcg(bgrp + base + ti) : -1ll;
+            } else if (q > 0) {
+              o_box[ti] = __ldcg(bbox + base - kTile + ti);
+              o_grp[ti] = __ldcg(bgrp + base - kTile + ti);
             }
             __syncthreads();
+            // (a) my share of the kept list (as of the start of this phase) against tile q
+            if (p >= 0) {
+              int n0;
+              asm volatile("ld.relaxed.gpu.s32 %0, [%1];" : "=r"(n0) : "l"(nk_pub + (p & 1)) : "memory");
+              const int lo = (int)((long long)n0 * tr / T), hi = (int)((long long)n0 * (tr + 1) / T);
+              const float4 box = q_box[ti];
+              const long long grp = q_grp[ti];
+              const float area = box_area(box);
+              bool hit = false;
+              for (int c0 = lo; c0 < hi; c0 += kStage) {
+                const int cnt = min(kStage, hi - c0);
+                for (int i = threadIdx.x; i < cnt; i += kBigThreads) {
+                  st_box[i] = __ldcg(kept_box + c0 + i);
+                  st_grp[i] = __ldcg(kept_grp + c0 + i);
+                }
+                __syncthreads();
+                if (ti < nt && !hit) {
+                  for (int k = half; k < cnt; k += 2) {
+                    const float4 kb = st_box[k];
+                    if (st_grp[k] == grp && suppresses(kb, box_area(kb), box, area, iou_thr)) {
+                      hit = true;
+                      break;
+                    }
+                  }
+                }
+                __syncthreads();
+              }
+              const unsigned m = __ballot_sync(0xffffffffu, hit);
+              if (lane == 0 && m) atomicOr(dead + (q & 1) * kTileWords + (wid & (kTileWords - 1)), m);
+            }
+            // (b) my share of the two bit matrices of tile q: one ballot per (row, 32-column word)
+            unsigned* m_in = big.mat + ((size_t)(g * 2 + (q & 1)) * 2 + 0) * (kTile * kTileWords);
+            unsigned* m_prev = big.mat + ((size_t)(g * 2 + (q & 1)) * 2 + 1) * (kTile * kTileWords);
+            const int per_mat = kTile * kTileWords;
+            const int nitems = (q > 0 ? 2 : 1) * per_mat;
+            for (int item = tr * (kBigThreads / 32) + wid; item < nitems; item += T * (kBigThreads / 32)) {
+              const int which = item / per_mat;
+              const int rr = (item - which * per_mat) / kTileWords;
+              const int w = item & (kTileWords - 1);
+              const int j = w * 32 + lane;
+              bool hit = false;
+              if (which == 0) {
+                if (w < (rr >> 5) || rr >= nt) continue;  // lower triangle / past the end: never read
+                if (j > rr && j < nt) {
+                  const float4 br = q_box[rr], bj = q_box[j];
+                  hit = q_grp[rr] == q_grp[j] && suppresses(br, box_area(br), bj, box_area(bj), iou_thr);
+                }
+                const unsigned m = __ballot_sync(0xffffffffu, hit);
+                if (lane == 0) m_in[rr * kTileWords + w] = m;
+              } else {
+                if (j < nt) {
+                  const float4 br = o_box[rr], bj = q_box[j];
+                  hit = o_grp[rr] == q_grp[j] && suppresses(br, box_area(br), bj, box_area(bj), iou_thr);
+                }
+                const unsigned m = __ballot_sync(0xffffffffu, hit);
+                if (lane == 0) m_prev[rr * kTileWords + w] = m;
+              }
+            }
           }
-          const unsigned m = __ballot_sync(0xffffffffu, hit);
-          if (lane == 0 && m) atomicOr(dead + ((p + 1) & 1) * kTileWords + (wid & (kTileWords - 1)), m);
+          group_sync(ctr, target, csz);
         }
-        if (csz > 1) group_sync(ctr, target, csz);
-        else __syncthreads();
       }
       if (r == 0 && threadIdx.x == 0) v.kept_count[seg] = nkept;
     }
@@ -1132,6 +1252,7 @@ static int launch_segments(YhWorkspace* ws, const P& prov, SegView v, int S, dou
   bv.sync = ws->big_sync;
   bv.dead = ws->big_sync + kBigGroups * 32;
   bv.nkept = (int*)(ws->big_sync + kBigGroups * 32 + kBigGroups * 2 * kTileWords);
+  bv.mat = ws->big_mat;
   YH_CUDA(cudaMemsetAsync(ws->big_sync, 0, YH_BIG_SYNC_WORDS * sizeof(unsigned), s));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)ws->num_sms);
@@ -1192,6 +1313,7 @@ int yh_nms(YhWorkspace* ws, const float* const* heads, const YhLayer* layers, in
              (long long)prov.t.N * C);
   cudaStream_t s = (cudaStream_t)stream;
   YH_CUDA(cudaSetDevice(ws->device));
+  note_batch(B);
   SegView v = make_view(ws);
   // instances per thread.  Sweep inside the overlapped step on B200 (r1f): 8 -> 193.1 us per step,
   // 4 -> 191.3, 2 -> 191.0, 1 -> 184.4..189.9 (kernel alone 46 / 38 / 36 / 35.5 us): many short
@@ -1244,6 +1366,7 @@ int yh_nms_by_scores(YhWorkspace* ws, const float* ltrb, const float* scores,
   YH_REQUIRE(K == 0 || next_pow2(K) <= room, "K=%d exceeds the workspace (%lld keys)", K, room);
   cudaStream_t s = (cudaStream_t)stream;
   YH_CUDA(cudaSetDevice(ws->device));
+  note_batch(1);
   if (K == 0) {
     YH_CUDA(cudaMemsetAsync(out_K_dev, 0, sizeof(int32_t), s));
     return YH_OK;

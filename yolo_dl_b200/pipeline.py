@@ -66,9 +66,12 @@ class DeviceStep:
         self._side = None
         self._pub_stream = None
         self._graph = None
-        # "grouped": the loss in L2-sized image ranges (run_grouped); "overlapped": round 1's
-        # fork/join of whole-batch kernels (run_overlapped)
-        self.schedule = os.environ.get("YH_SCHEDULE", "grouped")
+        # "overlapped": fork/join of whole-batch kernels (run_overlapped), the default; "grouped":
+        # the loss in L2-sized image ranges (run_grouped) — measured and NOT faster on B200 (r2:
+        # 318 / 230 us per step with groups of 8 / 16 images against 178: every ranged dense launch
+        # pays ~6 us of ramp-up and drain, and the rows kernel is latency-bound at ~19 us per launch
+        # however few rows it has), kept for A/B
+        self.schedule = os.environ.get("YH_SCHEDULE", "overlapped")
         self.kernels_in_graph = 0
 
     def algorithmic_bytes(self, matches=0, obj_pass=0, detections=0):
