@@ -3,12 +3,12 @@
 # schedule A/B, timelines, full bench line.  Every stage under its own timeout; logs in gpurun_out/.
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/gpu.txt 2>&1
-echo "### 1. single-group NMS"; timeout 300 python tools/nms_single_group.py 1 > gpurun_out/nms1.log 2>&1; echo "rc=$?"; tail -8 gpurun_out/nms1.log
+echo "### 1. single-group NMS"; timeout 300 python tools/nms_single_group.py 1 > gpurun_out/nms1.log 2>&1; echo "rc=$?"; tail -8 gpurun_out/nms1.log; timeout 300 python tools/nms_single_group.py 80 > gpurun_out/nms80.log 2>&1; echo "rc=$?"; tail -8 gpurun_out/nms80.log
 echo "### 2. smoke"; timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "rc=$?"; tail -3 gpurun_out/smoke.log
 echo "### 3. pytest -m gpu"; timeout 2700 python -m pytest tests -m gpu -q -s -p no:cacheprovider > gpurun_out/pytest_gpu.log 2>&1; echo "rc=$?"; tail -25 gpurun_out/pytest_gpu.log | cut -c1-300
 echo "### 4. schedule A/B (B=64)"
 B="python bench.py --steps 300 --warmup 10 --no-cpu-baseline --no-e2e --no-extras --no-strong --windows 3"
-for cfg in "YH_SCHEDULE=overlapped YH_PDL=0" "YH_SCHEDULE=overlapped" "YH_SCHEDULE=grouped YH_GROUP=8 YH_DENSE_AFTER=assign" "YH_SCHEDULE=grouped YH_GROUP=8 YH_DENSE_AFTER=fork" "YH_SCHEDULE=grouped YH_GROUP=16 YH_DENSE_AFTER=assign" "YH_SCHEDULE=grouped YH_GROUP=4 YH_DENSE_AFTER=assign" "YH_SCHEDULE=grouped YH_GROUP=8 YH_DENSE_AFTER=assign YH_L2_HINT=1" "YH_SCHEDULE=grouped YH_GROUP=8 YH_DENSE_AFTER=assign YH_DECODE_PER=8"; do
+for cfg in "YH_PDL=0" "YH_PDL=1" "YH_L2_HINT=1" "YH_DECODE_PER=8" "YH_L2_HINT=1 YH_DECODE_PER=8" "YH_SCHEDULE=grouped YH_GROUP=16 YH_DENSE_AFTER=fork"; do
   echo "== $cfg"
   env $cfg timeout 300 $B 2> gpurun_out/bench_err.log | python -c "
 import sys, json
@@ -22,11 +22,11 @@ for l in sys.stdin:
   tail -3 gpurun_out/bench_err.log
 done
 echo "### 5. timelines"
-for cfg in "YH_SCHEDULE=overlapped YH_PDL=0" "YH_SCHEDULE=overlapped YH_PDL=1" "YH_SCHEDULE=grouped YH_DENSE_AFTER=fork YH_PDL=1"; do
+for cfg in "YH_PDL=0" "YH_PDL=1"; do
   echo "== B=8 $cfg"
   env $cfg timeout 200 python tools/timeline.py --batch 8 --replays 30 2>&1 | tail -22
 done
-echo "== B=64 grouped(assign)"; timeout 200 python tools/timeline.py --batch 64 --replays 20 2>&1 | tail -36
+echo "== B=64 default"; timeout 200 python tools/timeline.py --batch 64 --replays 20 2>&1 | tail -16
 echo "### 6. full default bench"
 timeout 1200 python bench.py > gpurun_out/bench_full.json 2> gpurun_out/bench_full.err; echo "bench rc=$?"; tail -3 gpurun_out/bench_full.err
 python - <<'PY'
