@@ -226,11 +226,10 @@ struct YhWorkspace {
   int* by_ints;                   // yh_nms_by_scores buckets: count | off | cursor | kept | total
 
   // nms_big_kernel (segments above YH_BIG_MIN candidates); allocated when cand_per_image > YH_BIG_MIN
-  float4* big_box;                // [8 groups * big_len] boxes of the segment a CTA group works on
-  long long* big_grp;             // [8 groups * big_len]
-  long long big_len;              // = cand_stride
+  float4* big_box;                // [max_batch * cand_stride] sorted candidates' boxes, laid out like cand_key
+  long long* big_grp;             // [max_batch * cand_stride]
   unsigned* big_sync;             // barrier counters | cross-test masks | kept counts (YH_BIG_SYNC_WORDS)
-  unsigned* big_mat;              // [8 groups][2][2][512 * 16] suppression bit matrices of the tiles in flight
+  unsigned* big_mat;              // [YH_BIG_GROUPS][2][2][512 * 16] suppression bit matrices of the tiles in flight
   int* cand_need;                 // device: largest candidate count that exceeded the capacity
   int cand_need_host;             // its value at the last yh_read_counts
 
@@ -240,4 +239,5 @@ struct YhWorkspace {
 
 #define YH_PARTIALS_MAX 8192
 #define YH_BIG_MIN 4096          // candidates per segment above which the multi-CTA NMS kernel takes it
-#define YH_BIG_SYNC_WORDS 1024
+#define YH_BIG_GROUPS 64         // CTA groups nms_big_kernel may split into
+#define YH_BIG_SYNC_WORDS (YH_BIG_GROUPS * (32 + 32 + 2))

@@ -313,12 +313,12 @@ int yh_workspace_create(int device, int max_batch, int64_t max_instances, int ca
   YH_ALLOC(ws->by_ints, 2048 * sizeof(int));
   YH_ALLOC(ws->cand_need, 64);
   if (cand_per_image > YH_BIG_MIN) {
-    // staging of the multi-CTA NMS kernel: 8 CTA groups, each working on one big segment
-    ws->big_len = ws->cand_stride;
-    YH_ALLOC(ws->big_box, (size_t)8 * (size_t)ws->big_len * sizeof(float4));
-    YH_ALLOC(ws->big_grp, (size_t)8 * (size_t)ws->big_len * sizeof(long long));
+    // the multi-CTA NMS kernel: boxes of the candidates in sorted order (same layout as the key
+    // lists), barrier words and the bit matrices of the tiles in flight
+    YH_ALLOC(ws->big_box, cands * sizeof(float4));
+    YH_ALLOC(ws->big_grp, cands * sizeof(long long));
     YH_ALLOC(ws->big_sync, YH_BIG_SYNC_WORDS * sizeof(unsigned));
-    YH_ALLOC(ws->big_mat, (size_t)8 * 2 * 2 * 512 * 16 * sizeof(unsigned));
+    YH_ALLOC(ws->big_mat, (size_t)YH_BIG_GROUPS * 2 * 2 * 512 * 16 * sizeof(unsigned));
   }
   YH_ALLOC(ws->err_flag, 64);
 #undef YH_ALLOC

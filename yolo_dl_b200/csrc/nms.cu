@@ -522,13 +522,13 @@ nms_segment_kernel(const P prov, const SegView v, const double iou_thr) {
 // 65 536 candidates of ONE group: 617 ms on one CTA (round 1) -> a few ms.
 constexpr int kBigThreads = 1024;
 constexpr int kBigMin = YH_BIG_MIN;
-constexpr int kBigGroups = 8;
+constexpr int kBigGroups = 64;   // most CTA groups one launch splits into (YH_BIG_GROUPS in common.cuh)
+constexpr int kBigMinCtas = 4;   // fewest CTAs of a group: one resolver, three testers
 constexpr int kStage = 1024;  // kept boxes a tester CTA stages in shared memory per round (24 KB)
 
 struct BigView {
-  float4* box;        // [kBigGroups * len] boxes of the segment a group is working on, sorted order
-  long long* grp;     // [kBigGroups * len]
-  long long len;
+  float4* box;        // boxes of the candidates in sorted order, laid out like the key lists
+  long long* grp;     // (segment base + position): no per-group copy, any number of groups
   unsigned* sync;     // [kBigGroups * 32] barrier counters, zero at launch
   unsigned* dead;     // [kBigGroups * 2 * kTileWords] cross-test masks, zero at launch
   int* nkept;         // [kBigGroups * 2] kept count as of the start of a phase (double-buffered)
@@ -603,16 +603,17 @@ nms_big_kernel(const P prov, const SegView v, const int S, const BigView big,
   for (int k = 0; k < kBigThreads / 32; ++k) nbig += s_scan[k];
   __syncthreads();
   if (nbig == 0) return;
+  // few big segments: all SMs on each; many: up to kBigGroups groups of >= kBigMinCtas CTAs side
+  // by side (256 buckets of 6 000 rows ran as 32 rounds of 8 groups of 18 SMs in the first
+  // version: the testers idled, the 8 resolvers set the pace)
   const int G = (int)gridDim.x;
-  int ngroups = min(min(nbig, kBigGroups), max(G / 2, 1));
+  int ngroups = min(min(nbig, kBigGroups), max(G / kBigMinCtas, 1));
   const int csz = G / ngroups;              // CTAs per group
   const int g = (int)blockIdx.x / csz;      // my group
   const int r = (int)blockIdx.x - g * csz;  // my rank inside it
   if (g >= ngroups) return;                 // left-over CTAs
   unsigned* ctr = big.sync + g * 32;
   unsigned target = 0;
-  float4* bbox = big.box + (size_t)g * (size_t)big.len;
-  long long* bgrp = big.grp + (size_t)g * (size_t)big.len;
   unsigned* dead = big.dead + g * 2 * kTileWords;
   int* nk_pub = big.nkept + g * 2;
 
@@ -645,6 +646,8 @@ nms_big_kernel(const P prov, const SegView v, const int S, const BigView big,
       unsigned long long* kept_key = v.kept_key + seg_base;
       float4* kept_box = v.kept_box + seg_base;
       long long* kept_grp = v.kept_grp + seg_base;
+      float4* bbox = big.box + seg_base;
+      long long* bgrp = big.grp + seg_base;
 
       // ---- 1. merge sort (result in `keys`) -------------------------------------------------
       const int ntile = (K + kSortTile - 1) / kSortTile;
@@ -1248,7 +1251,6 @@ static int launch_segments(YhWorkspace* ws, const P& prov, SegView v, int S, dou
   BigView bv;
   bv.box = ws->big_box;
   bv.grp = ws->big_grp;
-  bv.len = ws->big_len;
   bv.sync = ws->big_sync;
   bv.dead = ws->big_sync + kBigGroups * 32;
   bv.nkept = (int*)(ws->big_sync + kBigGroups * 32 + kBigGroups * 2 * kTileWords);
