@@ -40,7 +40,8 @@ class YoloHotError(RuntimeError):
         self.text = text
 
 
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libyolohot.so")
+LIB_PATH = os.environ.get("YH_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "libyolohot.so")
+# (YH_LIB: A/B of two builds of the library on the same box, tools/ab_libs.sh)
 
 # every symbol include/yolohot.h declares: name -> (restype, argtypes)
 _PF = POINTER(c_void_p)

@@ -236,6 +236,7 @@ __device__ __forceinline__ void smem_passes(unsigned long long* s, const int n, 
 __device__ void sort_keys(unsigned long long* __restrict__ keys, const int K,
                           unsigned long long* s) {
   if (K <= 1) return;
+#ifndef YH_SEG_NO_RANKSORT
   if (K <= kNmsThreads) {
     // rank sort: keys are unique (the index is part of the key), so the sorted position of a key
     // is the number of smaller keys — K broadcast reads of shared memory per thread and two
@@ -256,6 +257,7 @@ __device__ void sort_keys(unsigned long long* __restrict__ keys, const int K,
     __syncthreads();
     return;
   }
+#endif
   int P = 2;
   while (P < K) P <<= 1;
   if (P <= kSortTile) {
@@ -466,10 +468,31 @@ nms_segment_kernel(const P prov, const SegView v, const double iou_thr) {
     __syncthreads();
 
     // ---- c. in-order walk, one warp ----------------------------------------------------------
+#ifdef YH_SEG_OLD_WALK
+    if (wid == 0) {
+      unsigned rem = (lane < nwords) ? ~(s_al[0][lane] & s_al[1][lane]) : ~0u;
+      unsigned keep = 0u;
+      for (int w = 0; w < nwords; ++w) {
+        unsigned cur = __shfl_sync(0xffffffffu, rem, w);
+        unsigned kw = 0u;
+        while (~cur) {
+          const int j = __ffs(~cur) - 1;
+          kw |= 1u << j;
+          const int r = w * 32 + j;
+          const unsigned mrow = (lane >= w && lane < nwords) ? mask[r * kTileWords + lane] : 0u;
+          rem |= mrow;
+          cur |= __shfl_sync(0xffffffffu, mrow, w) | ((2u << j) - 1u);
+        }
+        if (lane == w) keep = kw;
+      }
+      s_keep[lane] = keep;
+    }
+#else
     if (wid == 0) {
       const unsigned rem = (lane < nwords) ? ~(s_al[0][lane] & s_al[1][lane]) : ~0u;
       s_keep[lane] = walk_tile(mask, rem, nwords, lane);
     }
+#endif
     __syncthreads();
 
     // ---- d. append the kept candidates in order ----------------------------------------------
