@@ -29,16 +29,18 @@ struct AssignTab {
   double ah[YH_MAX_LAYERS][YH_MAX_ANCHORS], aw[YH_MAX_LAYERS][YH_MAX_ANCHORS];
 };
 
-// One (GT, layer, anchor) entry -> up to 5 cells (pred_target_matching.rs:87-150).
-// f(flat, dist_bits) is called for every in-range neighbour cell.
-template <typename F>
-__device__ __forceinline__ void for_each_cell(const AssignTab& t, int l, int a, double gcy,
-                                              double gcx, double gh, double gw, F f) {
+// One (GT, layer, anchor) entry -> up to 5 cells (pred_target_matching.rs:87-150): centre, top,
+// left, bottom, right.  Fills flat[k] / d2[k] (f64 bits of the squared distance between the GT
+// centre and the cell centre) for the cells that exist and returns their bit mask; static slot
+// indices, so the ten values stay in registers.
+__device__ __forceinline__ unsigned cells_of(const AssignTab& t, int l, int a, double gcy, double gcx,
+                                             double gh, double gw, int flat[5],
+                                             unsigned long long d2[5]) {
   // anchor-ratio filter (:139-150)
   const double ah = t.ah[l][a], aw = t.aw[l][a];
   const bool bounded = (gh / ah <= t.thresh) && (ah / gh <= t.thresh) && (gw / aw <= t.thresh) &&
                        (aw / gw <= t.thresh);
-  if (!bounded) return;
+  if (!bounded) return 0u;
   // Transform::from_sizes_exact(unit, feature): sy = H/1, ty = 0 - 0*sy; cy*sy + ty (:88-94,
   // bbox/src/transform.rs:16-37, bbox/src/cycxhw.rs:40-47)
   const double Hd = (double)t.H[l], Wd = (double)t.W[l];
@@ -49,23 +51,25 @@ __device__ __forceinline__ void for_each_cell(const AssignTab& t, int l, int a, 
   const double fy = floor(cy), fx = floor(cx);
   const long long row = (long long)fy, col = (long long)fx;
   const double cy_fract = cy - trunc(cy), cx_fract = cx - trunc(cx);  // f64::fract
-  long long rr[5], cc[5];
-  int n = 0;
-  rr[n] = row; cc[n] = col; ++n;                                         // centre
-  if (cy_fract < 0.5) { rr[n] = row - 1; cc[n] = col; ++n; }             // top
-  if (cx_fract < 0.5) { rr[n] = row; cc[n] = col - 1; ++n; }             // left
-  if (t.rect4 && cy_fract > 0.5) { rr[n] = row + 1; cc[n] = col; ++n; }  // bottom (Rect4)
-  if (t.rect4 && cx_fract > 0.5) { rr[n] = row; cc[n] = col + 1; ++n; }  // right  (Rect4)
-  for (int i = 0; i < n; ++i) {
-    if (rr[i] < 0 || rr[i] >= t.H[l] || cc[i] < 0 || cc[i] >= t.W[l]) continue;  // (:112-116)
+  const bool want[5] = {true, cy_fract < 0.5, cx_fract < 0.5, t.rect4 && cy_fract > 0.5,
+                        t.rect4 && cx_fract > 0.5};
+  const long long rr[5] = {row, row - 1, row, row + 1, row};
+  const long long cc[5] = {col, col, col - 1, col, col + 1};
+  unsigned mask = 0u;
+#pragma unroll
+  for (int i = 0; i < 5; ++i) {
+    flat[i] = 0;
+    d2[i] = 0ull;
+    if (!want[i] || rr[i] < 0 || rr[i] >= t.H[l] || cc[i] < 0 || cc[i] >= t.W[l]) continue;  // (:112-116)
     // distance of the GT centre to the cell centre, ratio units (:193-204)
     const double pcy = __dadd_rn((double)rr[i], 0.5) / Hd;
     const double pcx = __dadd_rn((double)cc[i], 0.5) / Wd;
     const double dy = __dsub_rn(gcy, pcy), dx = __dsub_rn(gcx, pcx);
-    const double d2 = __dadd_rn(__dmul_rn(dy, dy), __dmul_rn(dx, dx));
-    const int flat = t.start[l] + (int)cc[i] + t.W[l] * ((int)rr[i] + t.H[l] * a);
-    f(flat, (unsigned long long)__double_as_longlong(d2));
+    flat[i] = t.start[l] + (int)cc[i] + t.W[l] * ((int)rr[i] + t.H[l] * a);
+    d2[i] = (unsigned long long)__double_as_longlong(__dadd_rn(__dmul_rn(dy, dy), __dmul_rn(dx, dx)));
+    mask |= 1u << i;
   }
+  return mask;
 }
 
 // Slot-table invariant: between two yh_assign calls every slot of the workspace is EMPTY
@@ -101,40 +105,83 @@ assign_slots_kernel(const AssignTab t, const double* __restrict__ gt,
   int la_total = 0;
   for (int l = 0; l < t.L; ++l) la_total += t.A[l];
 
-  for (int pass = 0; pass < 2; ++pass) {
-    for (int base = 0; base < ng; base += kMaxGtSmem) {
-      const int chunk = min(kMaxGtSmem, ng - base);
-      __syncthreads();
-      for (int i = threadIdx.x; i < chunk * 4; i += kAssignThreads) {
-        const int g = i >> 2, k = i & 3;
-        s_gt[g][k] = gt[(size_t)(g0 + base + g) * 5 + k];
-      }
-      __syncthreads();
-      const int work = chunk * la_total;
-      for (int wi = threadIdx.x; wi < work; wi += kAssignThreads) {
-        const int g = wi / la_total;
-        int r = wi - g * la_total;
-        int l = 0;
-        while (r >= t.A[l]) { r -= t.A[l]; ++l; }
-        const double gh = s_gt[g][2], gw = s_gt[g][3];
-        // abs_diff_eq!(h, 0.0) with the default f64 epsilon (:65-68)
-        if (fabs(gh) <= 2.220446049250313e-16 || fabs(gw) <= 2.220446049250313e-16) continue;
-        const int gidx = base + g;
-        if (pass == 0) {
-          for_each_cell(t, l, r, s_gt[g][0], s_gt[g][1], gh, gw,
-                        [&](int flat, unsigned long long d) {
-                          atomicMin(&sd[flat], d);
-                          atomicOr(&bits[flat >> 5], 1u << (flat & 31));
-                        });
-        } else {
-          for_each_cell(t, l, r, s_gt[g][0], s_gt[g][1], gh, gw,
-                        [&](int flat, unsigned long long d) {
-                          if (__ldcg(&sd[flat]) == d) atomicMin(&sg[flat], gidx);
-                        });
-        }
-      }
+  if (ng <= kMaxGtSmem && ng * la_total <= kAssignThreads) {
+    // The usual case (<= 56 labels per image with 9 anchors): one (GT, layer, anchor) entry per
+    // thread.  The cells are computed ONCE (the f64 divisions are the arithmetic of this kernel)
+    // and pass B issues its <= 5 slot reads together instead of one dependent L2 round trip per
+    // cell: 14.4 -> (r2) us per call at 8 images, where this kernel heads the critical path.
+    __syncthreads();
+    for (int i = threadIdx.x; i < ng * 4; i += kAssignThreads) {
+      const int g = i >> 2, k = i & 3;
+      s_gt[g][k] = gt[(size_t)(g0 + g) * 5 + k];
     }
     __syncthreads();
+    int fl[5];
+    unsigned long long dd[5];
+    unsigned cm = 0u;
+    const int wi = threadIdx.x;
+    int gidx = 0;
+    if (wi < ng * la_total) {
+      const int g = wi / la_total;
+      int r = wi - g * la_total;
+      int l = 0;
+      while (r >= t.A[l]) { r -= t.A[l]; ++l; }
+      gidx = g;
+      const double gh = s_gt[g][2], gw = s_gt[g][3];
+      if (!(fabs(gh) <= 2.220446049250313e-16 || fabs(gw) <= 2.220446049250313e-16))
+        cm = cells_of(t, l, r, s_gt[g][0], s_gt[g][1], gh, gw, fl, dd);
+    }
+#pragma unroll
+    for (int i = 0; i < 5; ++i)
+      if ((cm >> i) & 1u) {
+        atomicMin(&sd[fl[i]], dd[i]);
+        atomicOr(&bits[fl[i] >> 5], 1u << (fl[i] & 31));
+      }
+    __syncthreads();
+    unsigned long long cur[5];
+#pragma unroll
+    for (int i = 0; i < 5; ++i) cur[i] = ((cm >> i) & 1u) ? __ldcg(&sd[fl[i]]) : 0ull;
+#pragma unroll
+    for (int i = 0; i < 5; ++i)
+      if (((cm >> i) & 1u) && cur[i] == dd[i]) atomicMin(&sg[fl[i]], gidx);
+    __syncthreads();
+  } else {
+    for (int pass = 0; pass < 2; ++pass) {
+      for (int base = 0; base < ng; base += kMaxGtSmem) {
+        const int chunk = min(kMaxGtSmem, ng - base);
+        __syncthreads();
+        for (int i = threadIdx.x; i < chunk * 4; i += kAssignThreads) {
+          const int g = i >> 2, k = i & 3;
+          s_gt[g][k] = gt[(size_t)(g0 + base + g) * 5 + k];
+        }
+        __syncthreads();
+        const int work = chunk * la_total;
+        for (int wi = threadIdx.x; wi < work; wi += kAssignThreads) {
+          const int g = wi / la_total;
+          int r = wi - g * la_total;
+          int l = 0;
+          while (r >= t.A[l]) { r -= t.A[l]; ++l; }
+          const double gh = s_gt[g][2], gw = s_gt[g][3];
+          // abs_diff_eq!(h, 0.0) with the default f64 epsilon (:65-68)
+          if (fabs(gh) <= 2.220446049250313e-16 || fabs(gw) <= 2.220446049250313e-16) continue;
+          const int gidx = base + g;
+          int fl[5];
+          unsigned long long dd[5];
+          const unsigned cm = cells_of(t, l, r, s_gt[g][0], s_gt[g][1], gh, gw, fl, dd);
+#pragma unroll
+          for (int i = 0; i < 5; ++i) {
+            if (!((cm >> i) & 1u)) continue;
+            if (pass == 0) {
+              atomicMin(&sd[fl[i]], dd[i]);
+              atomicOr(&bits[fl[i] >> 5], 1u << (fl[i] & 31));
+            } else if (__ldcg(&sd[fl[i]]) == dd[i]) {
+              atomicMin(&sg[fl[i]], gidx);
+            }
+          }
+        }
+      }
+      __syncthreads();
+    }
   }
 
   // matches of this image = occupied slots; publish the bitmap for the emit kernel

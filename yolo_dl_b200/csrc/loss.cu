@@ -498,7 +498,7 @@ __device__ __forceinline__ float hausdorff_metric(const Box4 p, const Box4 q, co
 //   phase B  the whole warp walks the rows: lanes across the C class channels (three per lane
 //            up to C = 96, the rest in a tail loop), class BCE forward + backward.
 // Every load of both phases is issued before the first value is consumed.
-constexpr int kRowsPerWarp = 8;
+constexpr int kRowsPerWarpMax = 8;  // the template parameter RPW of loss_rows_kernel: 8, or 2 for small batches
 constexpr int kClsRegs = 3;
 
 // An image range [b_lo, b_hi) of a batch (yh_loss_*_range): which rows of the (batch, flat)-sorted
@@ -525,6 +525,7 @@ __device__ __forceinline__ int first_row_of_image(const long long* __restrict__ 
 // of the same few images while their gradient lines are still in the 126 MB L2: the ~85 4-byte
 // stores of a row then land in resident lines (no read-modify-write through DRAM, no staging
 // buffer, no scatter kernel).
+template <int kRowsPerWarp>
 __global__ void __launch_bounds__(kRowThreads)
 loss_rows_kernel(const LayerTab t, const GradTab g, const LossParams p, const RowRange rr,
                  const long long* __restrict__ m_batch, const long long* __restrict__ m_flat,
@@ -1049,7 +1050,11 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
   int dense_grid = ws->num_sms * dense_cps;
   if (dense_grid > slot_room) dense_grid = slot_room;
   int row_grid = ws->num_sms * 4;  // resident in one wave; rows beyond that grid-stride
-  const int rows_per_cta = (kRowThreads / 32) * kRowsPerWarp;
+  // rows per warp: 8 amortises the scalar box part over the class part when there are rows to
+  // spare; a batch of <= 16 images has ~200 rows per image and is latency-bound — 2 rows per
+  // warp put four times as many warps on the same rows
+  const int rpw = B <= 16 ? 2 : kRowsPerWarpMax;
+  const int rows_per_cta = (kRowThreads / 32) * rpw;
   const int need = (capacity + rows_per_cta - 1) / rows_per_cta;
   if (row_grid > need) row_grid = need;
   if (row_grid < 1) row_grid = 1;
@@ -1123,10 +1128,13 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
     memset(&rg, 0, sizeof(rg));
     if (direct) rg = g;
     YH_TIME(YH_K_LOSS_ROWS, s);
-    YH_CUDA(launch_pdl(loss_rows_kernel, dim3(row_grid), dim3(kRowThreads), 0, s, tab, rg, p, rr,
-                       (const long long*)m_batch, (const long long*)m_flat, m_target,
-                       (const long long*)m_class, M_dev, capacity, iou_score_dev, pred_rows_dev,
-                       (want_grad && !direct) ? ws->row_grad : nullptr, ws->partials));
+#define YH_ROWS(RPW)                                                                            \
+  YH_CUDA(launch_pdl(loss_rows_kernel<RPW>, dim3(row_grid), dim3(kRowThreads), 0, s, tab, rg, p, rr, \
+                     (const long long*)m_batch, (const long long*)m_flat, m_target,             \
+                     (const long long*)m_class, M_dev, capacity, iou_score_dev, pred_rows_dev,  \
+                     (want_grad && !direct) ? ws->row_grad : nullptr, ws->partials))
+    if (rpw == 2) YH_ROWS(2); else YH_ROWS(8);
+#undef YH_ROWS
     YH_LAUNCHED(s);
   }
   if (phases & kPhaseFinish) {
