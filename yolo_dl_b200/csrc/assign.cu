@@ -203,8 +203,12 @@ assign_slots_kernel(const AssignTab t, const double* __restrict__ gt,
 
 // Ordered compaction of the occupied slots into the match list, sorted by (batch, flat);
 // puts every slot it reads back to EMPTY.
-constexpr int kEmitThreads = 256;
-constexpr int kEmitList = 2048;  // matches of one tile (256 words = 8192 instances) kept in smem
+// 1024 threads: one tile covers 32 768 instances, so every YOLOv4 head is ONE tile and the kernel
+// is three dependent memory round trips (counts + bitmap -> slot -> label row) instead of one
+// such chain per 8192 instances; under the dense store stream of the overlapped step a round
+// trip costs 2-3 us and this kernel sits on the step's critical path (r2: 38 us in-graph).
+constexpr int kEmitThreads = 1024;
+constexpr int kEmitList = 4096;  // matches of one tile (1024 words = 32 768 instances) kept in smem
 
 __global__ void __launch_bounds__(kEmitThreads)
 assign_emit_kernel(int N, int B, const int words, const double* __restrict__ gt,
@@ -218,14 +222,21 @@ assign_emit_kernel(int N, int B, const int words, const double* __restrict__ gt,
   __shared__ int s_warp[kEmitThreads / 32];
   __shared__ int s_base;
   __shared__ int s_list[kEmitList];
+  __shared__ int s_pref[kEmitThreads];       // exclusive prefix of the tile's words (overflow path)
+  __shared__ unsigned s_word[kEmitThreads];  // the tile's words (overflow path)
   griddep_launch();
   griddep_wait();
   const int b = blockIdx.x;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const unsigned* bits = slot_bits + (size_t)b * (size_t)words;
 
-  // offset of this image = sum of counts of earlier images
+  // everything that depends only on the slot kernel is requested together: the counts of the
+  // earlier images, this image's label offset and its first tile of bitmap words
   int part = 0;
   for (int i = threadIdx.x; i < b; i += kEmitThreads) part += img_count[i];
+  const unsigned w_first = ((int)threadIdx.x < words) ? bits[threadIdx.x] : 0u;
+  const int g0 = gt_off[b];
+  const int mine = img_count[b];
   for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
   if (lane == 0) s_warp[wid] = part;
   __syncthreads();
@@ -235,7 +246,7 @@ assign_emit_kernel(int N, int B, const int words, const double* __restrict__ gt,
     s_base = tot;
     img_off[b] = tot;  // first row of image b in the match list (yh_assign_image_offsets)
     if (b == B - 1) {
-      const int M = tot + img_count[b];
+      const int M = tot + mine;
       img_off[B] = M;
       *out_M = M;
       if (M > capacity) atomicOr(err_flag, 1);
@@ -243,15 +254,13 @@ assign_emit_kernel(int N, int B, const int words, const double* __restrict__ gt,
   }
   __syncthreads();
   int base = s_base;
-  if (img_count[b] == 0) return;  // block-uniform
-  const int g0 = gt_off[b];
+  if (mine == 0) return;  // block-uniform
   unsigned long long* sd = slot_dist + (size_t)b * (size_t)N;
   int* sg = slot_gt + (size_t)b * (size_t)N;
-  const unsigned* bits = slot_bits + (size_t)b * (size_t)words;
 
   for (int tile = 0; tile < words; tile += kEmitThreads) {
     const int wi = tile + threadIdx.x;
-    unsigned w = (wi < words) ? bits[wi] : 0u;
+    unsigned w = tile == 0 ? w_first : ((wi < words) ? bits[wi] : 0u);
     const int c = __popc(w);
     // exclusive scan of c over the CTA
     int incl = c;
@@ -273,11 +282,14 @@ assign_emit_kernel(int N, int B, const int words, const double* __restrict__ gt,
     // publish the flats of this tile in order, then one thread per match (no serial walk over
     // the bits of a word: every match costs two dependent L2 round trips, slot -> GT row)
     int lp = before + incl - c;
-    while (w) {
-      const int bit = __ffs(w) - 1;
-      w &= w - 1;
-      if (lp < kEmitList) s_list[lp] = wi * 32 + bit;
-      ++lp;
+    s_pref[threadIdx.x] = lp;
+    s_word[threadIdx.x] = w;
+    if (total <= kEmitList) {
+      while (w) {
+        const int bit = __ffs(w) - 1;
+        w &= w - 1;
+        s_list[lp++] = wi * 32 + bit;
+      }
     }
     __syncthreads();
     for (int j = threadIdx.x; j < total; j += kEmitThreads) {
@@ -285,16 +297,16 @@ assign_emit_kernel(int N, int B, const int words, const double* __restrict__ gt,
       if (total <= kEmitList) {
         flat = s_list[j];
       } else {
-        // overflow of the list (> kEmitList matches in 8192 instances): select the j-th set bit
-        int rem = j, k = tile;
-        for (;; ++k) {
-          const int pc = __popc(bits[k]);
-          if (rem < pc) break;
-          rem -= pc;
+        // more matches in the tile than the list holds (CSP-640 with 300 labels per image: ~20 000):
+        // the word of match j by binary search over the words' prefix, then its (j - prefix)-th bit
+        int lo = 0, hi = kEmitThreads - 1;  // last word whose exclusive prefix is <= j
+        while (lo < hi) {
+          const int mid = (lo + hi + 1) >> 1;
+          if (s_pref[mid] <= j) lo = mid; else hi = mid - 1;
         }
-        unsigned ww = bits[k];
-        for (int r = 0; r < rem; ++r) ww &= ww - 1;
-        flat = k * 32 + __ffs(ww) - 1;
+        unsigned ww = s_word[lo];
+        for (int r = j - s_pref[lo]; r > 0; --r) ww &= ww - 1;
+        flat = (tile + lo) * 32 + __ffs(ww) - 1;
       }
       const int pos = base + j;
       const int g = sg[flat];

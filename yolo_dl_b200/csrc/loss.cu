@@ -1053,7 +1053,12 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
   // rows per warp: 8 amortises the scalar box part over the class part when there are rows to
   // spare; a batch of <= 16 images has ~200 rows per image and is latency-bound — 2 rows per
   // warp put four times as many warps on the same rows
-  const int rpw = B <= 16 ? 2 : kRowsPerWarpMax;
+  static const int rpw_env = []() {  // sweep knob
+    const char* e = getenv("YH_ROWS_PER_WARP");
+    const int v = e ? atoi(e) : 0;
+    return (v == 2 || v == 4 || v == 8) ? v : 0;
+  }();
+  const int rpw = rpw_env ? rpw_env : (B <= 16 ? 2 : kRowsPerWarpMax);
   const int rows_per_cta = (kRowThreads / 32) * rpw;
   const int need = (capacity + rows_per_cta - 1) / rows_per_cta;
   if (row_grid > need) row_grid = need;
@@ -1133,7 +1138,7 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
                      (const long long*)m_batch, (const long long*)m_flat, m_target,             \
                      (const long long*)m_class, M_dev, capacity, iou_score_dev, pred_rows_dev,  \
                      (want_grad && !direct) ? ws->row_grad : nullptr, ws->partials))
-    if (rpw == 2) YH_ROWS(2); else YH_ROWS(8);
+    if (rpw == 2) YH_ROWS(2); else if (rpw == 4) YH_ROWS(4); else YH_ROWS(8);
 #undef YH_ROWS
     YH_LAUNCHED(s);
   }
