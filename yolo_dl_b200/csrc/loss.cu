@@ -537,6 +537,20 @@ loss_rows_kernel(const LayerTab t, const GradTab g, const LossParams p, const Ro
   griddep_wait();
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int warps = kRowThreads / 32;
+  // The match row of the warp's FIRST pass is requested together with the match count instead
+  // of after it (the lists hold `capacity` rows, so the read is in bounds whatever M is; it is
+  // used only once m < M is known): one dependent memory round trip less on the step's critical
+  // chain assign -> rows -> finish.
+  const int m_first = (blockIdx.x * warps + wid) * kRowsPerWarp + lane;
+  const bool pre = rr.b_hi < 0 && lane < kRowsPerWarp && m_first < capacity;
+  long long pre_b = 0, pre_f = 0, pre_c = 0;
+  float4 pre_t = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (pre) {
+    pre_b = m_batch[m_first];
+    pre_f = m_flat[m_first];
+    pre_c = m_class[m_first];
+    pre_t = *reinterpret_cast<const float4*>(m_target + (size_t)m_first * 4);
+  }
   const int M = min(*M_dev, capacity);
   const bool direct = g.grad[0] != nullptr;
   const bool want_grad = row_grad != nullptr || direct;
@@ -569,10 +583,11 @@ loss_rows_kernel(const LayerTab t, const GradTab g, const LossParams p, const Ro
     int es = 0, l = 0, cls = 0, anchor = 0, row = 0, col = 0;
     float4 tg = make_float4(0.f, 0.f, 0.f, 0.f);
     if (own) {
-      const int b = (int)m_batch[m];
-      const int flat = (int)m_flat[m];
-      cls = (int)m_class[m];
-      tg = *reinterpret_cast<const float4*>(m_target + (size_t)m * 4);
+      const bool first = pre && m == m_first;
+      const int b = (int)(first ? pre_b : m_batch[m]);
+      const int flat = (int)(first ? pre_f : m_flat[m]);
+      cls = (int)(first ? pre_c : m_class[m]);
+      tg = first ? pre_t : *reinterpret_cast<const float4*>(m_target + (size_t)m * 4);
       const Cell c = locate(t, flat);
       l = c.layer;
       anchor = c.anchor;
