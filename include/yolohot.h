@@ -234,6 +234,27 @@ int yh_loss_rows_range(YhWorkspace* ws, const float* const* heads, const YhLayer
 int yh_loss_finish_ranges(YhWorkspace* ws, const YhLayer* layers, int L, int B, int C,
                           int num_ranges, const int32_t* M_dev, int capacity, const YhLossCfg* cfg,
                           float* losses4_dev, void* stream);
+/* The same loss cut by LAYER (yolo_dl_b200/pipeline.py, schedule "layered"): the gradient tensors
+ * of the small layers fit the 126 MB L2, the big first layer does not, and the gradient scatter
+ * of the matched rows (yh_loss_finish) costs a DRAM read-modify-write per line once the dense
+ * stream has evicted it.  So
+ *   yh_loss_dense_layers   the dense pass over layers [layer_lo, layer_hi) only (launch
+ *                          part_index of num_parts <= 16: its partial sums go to their own slots);
+ *   yh_loss_finish_layers  ordered after yh_loss_rows_compute (ONE whole-batch launch, same
+ *                          capacity / cfg) and after the dense launches of those layers: scatters
+ *                          the staged gradients of the matched rows that lie in layers
+ *                          [layer_lo, layer_hi); the launch with reduce != 0 must come after ALL
+ *                          dense launches and also writes losses4_dev.
+ * A caller runs finish(layer l) right behind dense(layer l) while dense(l+1 ..) streams on.
+ * Results are yh_loss_fwd_bwd's: gradients bit for bit, the scalars to f32 rounding. */
+int yh_loss_dense_layers(YhWorkspace* ws, const float* const* heads, const YhLayer* layers, int L,
+                         int B, int C, int layer_lo, int layer_hi, int part_index, int num_parts,
+                         const YhLossCfg* cfg, float* const* grad_heads, void* stream);
+int yh_loss_finish_layers(YhWorkspace* ws, const YhLayer* layers, int L, int B, int C, int layer_lo,
+                          int layer_hi, int reduce, int num_dense_parts, const int64_t* m_batch,
+                          const int64_t* m_flat, const int32_t* M_dev, int capacity,
+                          const YhLossCfg* cfg, float* losses4_dev, float* const* grad_heads,
+                          void* stream);
 /* Device pointer to the [B+1] int32 first-row-of-image offsets of the match list the last yh_assign
  * on this workspace produced (valid once that call has run on the stream). */
 const int32_t* yh_assign_image_offsets(const YhWorkspace* ws);

@@ -150,6 +150,44 @@ def test_grouped_schedule_equals_sequential(dev, name, B, group, monkeypatch):
         assert rc == yh._lib.YH_ERR_INVALID and b"multiple of 4" in step.lib.yh_last_error()
 
 
+@pytest.mark.parametrize("name,B", [("small", 5), ("yolov4_608", 6), ("yolov4_tiny_416", 9)])
+def test_layered_schedule_equals_sequential(dev, name, B):
+    """The loss cut by layer (yh_loss_dense_layers per layer, yh_loss_finish_layers of a layer right
+    behind its dense pass, the last one reducing): every output bit-identical to the one-sequence
+    form except the four loss scalars (differently associated f64 partial sums)."""
+    spec = synth.small_spec() if name == "small" else getattr(synth, name)()
+    om_, cm_ = (-2.0, -1.0) if name == "small" else (-3.5, -2.5)
+    heads = [h.to(dev) for h in synth.make_heads(spec, B, synth.SEED0 + 7, obj_mean=om_, cls_mean=cm_)]
+    targets = synth.make_targets(spec, B, synth.SEED0 + 7, n_max=12, clustered=0.3)
+    targets[0] = []
+    gt_h, off_h = yh.pack_labels(targets)
+    gt, off = gt_h.to(dev), off_h.to(dev)
+    step = DeviceStep(spec, B, dev, nms_conf=0.3, nms_iou=0.5, by_class=False)
+    step.run(heads, gt, off)
+    seq = snapshot(step)
+
+    def check():
+        got = snapshot(step)
+        torch.testing.assert_close(got["losses"], seq["losses"], rtol=2e-7, atol=0)
+        got["losses"] = seq["losses"]
+        same(seq, got)
+
+    for g in step.grads:
+        g.fill_(float("nan"))
+    step.losses4.fill_(float("nan"))
+    step.run_layered(heads, gt, off)
+    check()
+    step.schedule = "layered"
+    step.capture(heads, gt, off)
+    assert step.kernels_in_graph == step.expected_kernels()
+    for _ in range(2):
+        for g in step.grads:
+            g.fill_(float("nan"))
+        step.losses4.fill_(float("nan"))
+        step.replay()
+        check()
+
+
 def test_graph_replay_follows_refilled_inputs(dev):
     spec = synth.small_spec()
     B = 4

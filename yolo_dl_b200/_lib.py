@@ -78,6 +78,11 @@ SYMBOLS = {
                                    c_void_p, POINTER(YhLossCfg), c_void_p, c_void_p, _PF, c_void_p]),
     "yh_loss_finish_ranges": (c_int, [c_void_p, POINTER(YhLayer), c_int, c_int, c_int, c_int, c_void_p,
                                       c_int, POINTER(YhLossCfg), c_void_p, c_void_p]),
+    "yh_loss_dense_layers": (c_int, [c_void_p, _PF, POINTER(YhLayer), c_int, c_int, c_int, c_int, c_int,
+                                     c_int, c_int, POINTER(YhLossCfg), _PF, c_void_p]),
+    "yh_loss_finish_layers": (c_int, [c_void_p, POINTER(YhLayer), c_int, c_int, c_int, c_int, c_int, c_int,
+                                      c_int, c_void_p, c_void_p, c_void_p, c_int, POINTER(YhLossCfg),
+                                      c_void_p, _PF, c_void_p]),
     "yh_assign_image_offsets": (c_void_p, [c_void_p]),
     "yh_nms": (c_int, [c_void_p, _PF, POINTER(YhLayer), c_int, c_int, c_int, c_double, c_double,
                        c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,

@@ -791,7 +791,8 @@ loss_finish_kernel(const LayerTab t, const GradTab g, const LossParams p,
                    const int* __restrict__ M_dev, const int capacity,
                    const float* __restrict__ row_grad, const double* __restrict__ partials,
                    const int dense_per_range, const int rows_per_range, const int num_ranges,
-                   const int range_stride, float* __restrict__ losses4,
+                   const int num_row_ranges, const int range_stride, const int layer_lo,
+                   const int layer_hi, const int do_reduce, float* __restrict__ losses4,
                    int* __restrict__ err_flag) {
   griddep_launch();
   griddep_wait();
@@ -819,6 +820,7 @@ loss_finish_kernel(const LayerTab t, const GradTab g, const LossParams p,
       const int flat = __shfl_sync(0xffffffffu, nflat, 3);
       const Cell c = locate(t, flat);
       const int l = c.layer;
+      if (l < layer_lo || l >= layer_hi) continue;  // another launch's layers (yh_loss_finish_layers)
       const int esi = t.A[l] * t.HW[l];
       const size_t es = (size_t)esi;
       const int j = flat - t.start[l];  // position inside the entry run
@@ -867,7 +869,7 @@ loss_finish_kernel(const LayerTab t, const GradTab g, const LossParams p,
       }
     }
   }
-  if (blockIdx.x != 0) return;
+  if (blockIdx.x != 0 || !do_reduce) return;
 
   // CTA 0: fixed-order final sums
   __shared__ double s_red[kFinishThreads][4];
@@ -876,7 +878,7 @@ loss_finish_kernel(const LayerTab t, const GradTab g, const LossParams p,
   constexpr int kFinalUnroll = 8;
   // launch r of a ranged loss (yh_loss_*_range) wrote its partials from slot r * range_stride
   const int n_dense_partials = dense_per_range * num_ranges;
-  const int n_row_partials = rows_per_range * num_ranges;
+  const int n_row_partials = rows_per_range * num_row_ranges;
   double r[4] = {0.0, 0.0, 0.0, 0.0};
   for (int i0 = threadIdx.x; i0 < n_dense_partials; i0 += kFinishThreads * kFinalUnroll) {
     double v[kFinalUnroll];
@@ -955,6 +957,9 @@ struct LossRange {
   int b_lo, b_hi, index, count;
   const int32_t* img_off;  // per-image row offsets of the match list ([B+1], device) or null
   int direct;              // rows phase: scatter straight into grad_heads (no staging, no finish scatter)
+  int layer_lo, layer_hi;  // dense / finish phase: only these layers (layer_hi <= 0: all)
+  int finish_reduce;       // finish phase: also reduce the partial sums (the LAST finish launch)
+  int row_ranges;          // finish phase: launches of the rows phase (1: one whole-batch launch)
 };
 constexpr int kMaxRanges = 16;
 constexpr int kRangeSlots = kPartHalf / kMaxRanges;  // partial-sum slots per ranged launch
@@ -1078,7 +1083,8 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
   const int need = (capacity + rows_per_cta - 1) / rows_per_cta;
   if (row_grid > need) row_grid = need;
   if (row_grid < 1) row_grid = 1;
-  if (row_grid > slot_room) row_grid = slot_room;
+  const bool rows_whole = ranged && range->row_ranges == 1;  // layered finish after a plain rows launch
+  if (row_grid > (rows_whole ? kPartHalf : slot_room)) row_grid = rows_whole ? kPartHalf : slot_room;
   const int part_off = ranged ? range->index * kRangeSlots : 0;
 
   if (phases & kPhaseDense) {
@@ -1086,28 +1092,42 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
     // pointers advanced by b_lo images (the loss is normalised by the WHOLE batch: numel)
     const int b_lo = ranged ? range->b_lo : 0;
     const int Bd = ranged ? range->b_hi - range->b_lo : B;
+    // ... and/or only the layers [layer_lo, layer_hi) (yh_loss_dense_layers): the kernel walks
+    // compacted tables, so a subset is just a shorter layer list
+    const int l_lo = (ranged && range->layer_hi > 0) ? range->layer_lo : 0;
+    const int l_hi = (ranged && range->layer_hi > 0) ? range->layer_hi : L;
+    YH_REQUIRE(l_lo >= 0 && l_lo < l_hi && l_hi <= L, "layers [%d,%d) outside 0..%d", l_lo, l_hi, L);
     LayerTab dt_tab = tab;
-    GradTab dg = g;
+    GradTab dg;
+    memset(&dg, 0, sizeof(dg));
     DenseTab dt;
     memset(&dt, 0, sizeof(dt));
-    dt.L = L;
-    for (int l = 0; l < YH_MAX_LAYERS; ++l) {
+    dt.L = l_hi - l_lo;
+    dt_tab.L = l_hi - l_lo;
+    for (int k = 0; k < YH_MAX_LAYERS; ++k) {
       long long tiles = 0, oq = 0;
-      if (l < L) {
-        dt.run[l] = (long long)tab.A[l] * tab.HW[l];
-        const long long shift = (long long)b_lo * dt.run[l] * tab.E;  // floats
+      const int l = l_lo + k;
+      if (l < l_hi) {
+        dt.run[k] = (long long)tab.A[l] * tab.HW[l];
+        const long long shift = (long long)b_lo * dt.run[k] * tab.E;  // floats
         YH_REQUIRE(shift % 4 == 0,
                    "b_lo=%d: layer %d has %lld floats per image, an image range must start at a "
                    "16-byte boundary of every head tensor (use a multiple of 4 images)",
-                   b_lo, l, dt.run[l] * tab.E);
-        dt_tab.head[l] = tab.head[l] + shift;
-        if (grad_heads) dg.grad[l] = g.grad[l] + shift;
-        const long long quads = ((long long)Bd * dt.run[l] * tab.E + 3) / 4;
+                   b_lo, l, dt.run[k] * tab.E);
+        dt_tab.H[k] = tab.H[l];
+        dt_tab.W[k] = tab.W[l];
+        dt_tab.A[k] = tab.A[l];
+        dt_tab.HW[k] = tab.HW[l];
+        dt_tab.head[k] = tab.head[l] + shift;
+        if (grad_heads) dg.grad[k] = g.grad[l] + shift;
+        const long long quads = ((long long)Bd * dt.run[k] * tab.E + 3) / 4;
         tiles = (quads + kTileQuads - 1) / kTileQuads;
-        oq = (long long)Bd * (dt.run[l] / 4 + 2);
+        oq = (long long)Bd * (dt.run[k] / 4 + 2);
+      } else {
+        dt_tab.head[k] = nullptr;
       }
-      dt.tile_prefix[l + 1] = dt.tile_prefix[l] + tiles;
-      dt.qprefix[l + 1] = dt.qprefix[l] + oq;
+      dt.tile_prefix[k + 1] = dt.tile_prefix[k] + tiles;
+      dt.qprefix[k + 1] = dt.qprefix[k] + oq;
     }
     // with a gradient: dense_grid objectness CTAs followed by one CTA per 32 KB tile
     const long long dense_tiles = dt.tile_prefix[YH_MAX_LAYERS];
@@ -1167,8 +1187,12 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
     YH_CUDA(launch_pdl(loss_finish_kernel, dim3(fin_grid), dim3(kFinishThreads), 0, s, tab, g, p,
                        (const long long*)m_batch, (const long long*)m_flat, M_dev, capacity,
                        grad_heads ? (const float*)ws->row_grad : (const float*)nullptr,
-                       (const double*)ws->partials, dense_grid, row_grid, num_ranges, kRangeSlots,
-                       losses4_dev, ws->err_flag));
+                       (const double*)ws->partials, dense_grid, row_grid, num_ranges,
+                       (ranged && range->row_ranges > 0) ? range->row_ranges : num_ranges, kRangeSlots,
+                       (ranged && range->layer_hi > 0) ? range->layer_lo : 0,
+                       (ranged && range->layer_hi > 0) ? range->layer_hi : YH_MAX_LAYERS,
+                       (ranged && range->layer_hi > 0) ? range->finish_reduce : 1, losses4_dev,
+                       ws->err_flag));
     YH_LAUNCHED(s);
   }
   return YH_OK;
@@ -1233,7 +1257,7 @@ int yh_loss_dense_range(YhWorkspace* ws, const float* const* heads, const YhLaye
                         int B, int C, int b_lo, int b_hi, int range_index, int num_ranges,
                         const YhLossCfg* cfg, float* const* grad_heads, void* stream) {
   YH_REQUIRE(heads != nullptr, "heads is NULL");
-  yh::LossRange r = {b_lo, b_hi, range_index, num_ranges, nullptr, 0};
+  yh::LossRange r = {b_lo, b_hi, range_index, num_ranges, nullptr, 0, 0, 0, 1, 0};
   YH_REQUIRE(num_ranges >= 1, "num_ranges=%d", num_ranges);
   return yh::loss_phases(yh::kPhaseDense, ws, heads, layers, L, B, C, nullptr, nullptr, nullptr,
                          nullptr, nullptr, 0, cfg, nullptr, nullptr, nullptr, grad_heads, 0, stream,
@@ -1249,7 +1273,7 @@ int yh_loss_rows_range(YhWorkspace* ws, const float* const* heads, const YhLayer
                        void* stream) {
   YH_REQUIRE(heads != nullptr, "heads is NULL");
   YH_REQUIRE(num_ranges >= 1, "num_ranges=%d", num_ranges);
-  yh::LossRange r = {b_lo, b_hi, range_index, num_ranges, image_row_offsets_dev, 1};
+  yh::LossRange r = {b_lo, b_hi, range_index, num_ranges, image_row_offsets_dev, 1, 0, 0, 1, 0};
   return yh::loss_phases(yh::kPhaseRows, ws, heads, layers, L, B, C, m_batch, m_flat, m_target,
                          m_class, M_dev, capacity, cfg, nullptr, iou_score_dev, pred_rows_dev,
                          grad_heads, 0, stream, &r);
@@ -1259,9 +1283,34 @@ int yh_loss_finish_ranges(YhWorkspace* ws, const YhLayer* layers, int L, int B, 
                           int num_ranges, const int32_t* M_dev, int capacity, const YhLossCfg* cfg,
                           float* losses4_dev, void* stream) {
   YH_REQUIRE(num_ranges >= 1, "num_ranges=%d", num_ranges);
-  yh::LossRange r = {0, B, 0, num_ranges, nullptr, 1};
+  yh::LossRange r = {0, B, 0, num_ranges, nullptr, 1, 0, 0, 1, 0};
   return yh::loss_phases(yh::kPhaseFinish, ws, nullptr, layers, L, B, C, nullptr, nullptr, nullptr,
                          nullptr, M_dev, capacity, cfg, losses4_dev, nullptr, nullptr, nullptr, 0,
+                         stream, &r);
+}
+
+// ---- layered forms: the dense pass cut by LAYER, the scatter of a layer group behind it ------
+int yh_loss_dense_layers(YhWorkspace* ws, const float* const* heads, const YhLayer* layers, int L,
+                         int B, int C, int layer_lo, int layer_hi, int part_index, int num_parts,
+                         const YhLossCfg* cfg, float* const* grad_heads, void* stream) {
+  YH_REQUIRE(heads != nullptr, "heads is NULL");
+  YH_REQUIRE(num_parts >= 1 && layer_hi > 0, "num_parts=%d layer_hi=%d", num_parts, layer_hi);
+  yh::LossRange r = {0, B, part_index, num_parts, nullptr, 0, layer_lo, layer_hi, 0, 0};
+  return yh::loss_phases(yh::kPhaseDense, ws, heads, layers, L, B, C, nullptr, nullptr, nullptr,
+                         nullptr, nullptr, 0, cfg, nullptr, nullptr, nullptr, grad_heads, 0, stream,
+                         &r);
+}
+
+int yh_loss_finish_layers(YhWorkspace* ws, const YhLayer* layers, int L, int B, int C, int layer_lo,
+                          int layer_hi, int reduce, int num_dense_parts, const int64_t* m_batch,
+                          const int64_t* m_flat, const int32_t* M_dev, int capacity,
+                          const YhLossCfg* cfg, float* losses4_dev, float* const* grad_heads,
+                          void* stream) {
+  YH_REQUIRE(num_dense_parts >= 1 && layer_hi > 0 && layer_lo >= 0 && layer_lo < layer_hi && layer_hi <= L,
+             "num_dense_parts=%d layers [%d,%d)", num_dense_parts, layer_lo, layer_hi);
+  yh::LossRange r = {0, B, 0, num_dense_parts, nullptr, 0, layer_lo, layer_hi, reduce ? 1 : 0, 1};
+  return yh::loss_phases(yh::kPhaseFinish, ws, nullptr, layers, L, B, C, m_batch, m_flat, nullptr,
+                         nullptr, M_dev, capacity, cfg, losses4_dev, nullptr, nullptr, grad_heads, 0,
                          stream, &r);
 }
 

@@ -468,7 +468,9 @@ nms_segment_kernel(const P prov, const SegView v, const double iou_thr) {
     __syncthreads();
 
     // ---- c. in-order walk, one warp ----------------------------------------------------------
-#ifdef YH_SEG_OLD_WALK
+    // (the register walk of nms_big_kernel, walk_tile, is NOT used here: inside the overlapped
+    // training step it made this kernel 42 us instead of 33 and the step 193 us instead of 177-180
+    // — same-box A/B of the two libraries, profiles/r2_ab_libs.txt — although alone both take 22.7 us)
     if (wid == 0) {
       unsigned rem = (lane < nwords) ? ~(s_al[0][lane] & s_al[1][lane]) : ~0u;
       unsigned keep = 0u;
@@ -487,12 +489,6 @@ nms_segment_kernel(const P prov, const SegView v, const double iou_thr) {
       }
       s_keep[lane] = keep;
     }
-#else
-    if (wid == 0) {
-      const unsigned rem = (lane < nwords) ? ~(s_al[0][lane] & s_al[1][lane]) : ~0u;
-      s_keep[lane] = walk_tile(mask, rem, nwords, lane);
-    }
-#endif
     __syncthreads();
 
     // ---- d. append the kept candidates in order ----------------------------------------------
