@@ -238,6 +238,7 @@ struct YhWorkspace {
 };
 
 #define YH_PARTIALS_MAX 8192
-#define YH_BIG_MIN 4096          // candidates per segment above which the multi-CTA NMS kernel takes it
+#define YH_BIG_MIN 1024          // candidates per segment above which the multi-CTA NMS kernel takes it
+                                 // (one group of 1000 rows: 0.59 ms on one CTA; 5000 rows on all SMs: 0.60 ms)
 #define YH_BIG_GROUPS 64         // CTA groups nms_big_kernel may split into
 #define YH_BIG_SYNC_WORDS (YH_BIG_GROUPS * (32 + 32 + 2))

@@ -112,6 +112,11 @@ __device__ __forceinline__ bool suppresses(const float4 a, const float area_a, c
   const float xx1 = fmaxf(a.y, c.y), yy1 = fmaxf(a.x, c.x);
   const float xx2 = fminf(a.w, c.w), yy2 = fminf(a.z, c.z);
   const float w = fmaxf(0.0f, xx2 - xx1), h = fmaxf(0.0f, yy2 - yy1);
+  // disjoint boxes (most pairs): inter = 0, so the quotient is 0 or 0/0 = NaN and neither is
+  // > thr for a non-negative threshold (a negative one takes the full path) — same answer, no division
+  // (the IEEE division is a third of this function; the kept-list test of the large-segment
+  // kernel is bound by exactly this arithmetic on all SMs)
+  if (!(w > 0.0f && h > 0.0f) && thr >= 0.0) return false;
   const float inter = w * h;
   const float ovr = inter / (area_a + area_c - inter);
   return (double)ovr > thr;

@@ -21,7 +21,7 @@ from .workspace import Workspace
 
 class DeviceStep:
     def __init__(self, spec, batch: int, device: torch.device, loss: YoloLossInit = None,
-                 nms_conf=0.4, nms_iou=0.5, by_class=True, max_gt=None, cand_per_image=4096,
+                 nms_conf=0.4, nms_iou=0.5, by_class=True, max_gt=None, cand_per_image=1024,
                  max_detections=None, with_grad=True):
         self.lib = _lib.load()
         self.spec, self.B, self.dev = spec, batch, device
@@ -92,7 +92,7 @@ class DeviceStep:
         the loss: dense + rows + finish, or per image range dense + rows, then one finish."""
         grouped = (self.schedule == "grouped" and self._grad_ptrs is not None and self.B >= 8) \
             if grouped is None else grouped
-        base = 6 + (1 if self.ws.key[3] > 4096 else 0)
+        base = 6 + (1 if self.ws.key[3] > 1024 else 0)   # YH_BIG_MIN
         if self.schedule == "layered" and self._grad_ptrs is not None and self.L >= 2 and not grouped:
             return base + 1 + 2 * self.L
         if not grouped:
