@@ -8,7 +8,7 @@ echo "### 2. smoke"; timeout 300 python -c "import __graft_entry__ as g; g.smoke
 echo "### 3. pytest -m gpu"; timeout 2700 python -m pytest tests -m gpu -q -s -p no:cacheprovider > gpurun_out/pytest_gpu.log 2>&1; echo "rc=$?"; tail -25 gpurun_out/pytest_gpu.log | cut -c1-300
 echo "### 4. schedule A/B (B=64)"
 B="python bench.py --steps 300 --warmup 10 --no-cpu-baseline --no-e2e --no-extras --no-strong --windows 3"
-for cfg in "YH_SCHEDULE=overlapped" "YH_SCHEDULE=layered" "YH_SCHEDULE=layered YH_NMS_PRIO=0" "YH_SCHEDULE=overlapped YH_NMS_PRIO=0" "YH_SCHEDULE=layered YH_ROWS_PER_WARP=4" "YH_SCHEDULE=layered YH_ROWS_PER_WARP=2" "YH_SCHEDULE=layered YH_PDL=1" "YH_SCHEDULE=overlapped"; do
+for cfg in "YH_SCHEDULE=overlapped" "YH_ROWS_PER_WARP=4" "YH_ROWS_PER_WARP=2" "YH_L2_HINT=1" "YH_SCHEDULE=overlapped"; do
   echo "== $cfg"
   env $cfg timeout 300 $B 2> gpurun_out/bench_err.log | python -c "
 import sys, json
@@ -27,7 +27,6 @@ for cfg in "YH_PDL=0" "YH_PDL=1"; do
   env $cfg timeout 200 python tools/timeline.py --batch 8 --replays 30 2>&1 | tail -22
 done
 echo "== B=64 overlapped"; timeout 200 python tools/timeline.py --batch 64 --replays 20 2>&1 | tail -16
-echo "== B=64 layered"; YH_SCHEDULE=layered timeout 200 python tools/timeline.py --batch 64 --replays 20 2>&1 | tail -20
 echo "### 6. full default bench"
 timeout 1200 python bench.py > gpurun_out/bench_full.json 2> gpurun_out/bench_full.err; echo "bench rc=$?"; tail -3 gpurun_out/bench_full.err
 python - <<'PY'

@@ -675,7 +675,7 @@ nms_big_kernel(const P prov, const SegView v, const int S, const BigView big,
 
       // ---- 1. merge sort (result in `keys`) -------------------------------------------------
       const int ntile = (K + kSortTile - 1) / kSortTile;
-      const int Kp = ntile * kSortTile;  // the segment has room for it: power-of-two >= 8192
+      const int Kp = ntile * kSortTile;  // merge passes only when ntile > 1: then Kp <= next_pow2(K), the segment's room
       int npass = 0;
       for (int run = 1; run < ntile; run <<= 1) ++npass;
       unsigned long long* src = (npass & 1) ? kept_key : keys;
@@ -686,7 +686,11 @@ nms_big_kernel(const P prov, const SegView v, const int S, const BigView big,
           s_keys[i] = (base + i < K) ? keys[base + i] : ~0ull;
         __syncthreads();
         for (int k = 2; k <= kSortTile; k <<= 1) smem_passes(s_keys, kSortTile, 0, k, k >> 1);
-        for (int i = threadIdx.x; i < kSortTile; i += kBigThreads) src[base + i] = s_keys[i];
+        // several tiles: the padding keys of the last tile are written too (the merges read them;
+        // Kp <= the segment's power-of-two room once K > kSortTile).  ONE tile: only the K real
+        // keys go back — a segment of 1025..8191 candidates has room for next_pow2(K) < 8192 only
+        const int nwrite = ntile > 1 ? kSortTile : K;
+        for (int i = threadIdx.x; i < nwrite; i += kBigThreads) src[base + i] = s_keys[i];
         __syncthreads();
       }
       group_sync(ctr, target, csz);
