@@ -837,35 +837,54 @@ loss_finish_kernel(const LayerTab t, const GradTab g, const LossParams p,
       for (int k = 0; k < 7; ++k) d[k] = __shfl_sync(0xffffffffu, dk, k);
       float* gp = g.grad[l] + head_offset(t, l, b, c.anchor, c.cell);
       const float* src = row_grad + (size_t)m * t.E;
-      for (int e = lane; e < t.E; e += 32) {
-        const float v = __ldcs(src + e);
-        const long long q = ((long long)b * t.E + e) * (long long)es + j;  // float index in the tensor
-        const int a = (int)(q & 3);
-        if (e == 4 || j - a < 0 || j - a + 3 >= esi) {
-          gp[(size_t)e * es] = v;
-          continue;
+      // All loads of a row first, then the stores: the staged values of this row at its (up to)
+      // three entries per lane AND those of rows m+1..m+3 wherever they are neighbours (needed
+      // only where they share a quad, fetched regardless: 12 independent loads instead of three
+      // rounds of load -> test -> dependent load).  This kernel is latency-bound (ncu: DRAM 16 %,
+      // SM 20 % busy, r1f) and runs ALONE at the tail of the overlapped step.
+      for (int e0 = 0; e0 < t.E; e0 += 96) {
+        float v[3], vn[3][3];
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+          const int e = e0 + lane + 32 * i;
+          const bool ok = e < t.E;
+          v[i] = ok ? __ldcs(src + e) : 0.0f;
+#pragma unroll
+          for (int k = 0; k < 3; ++k)
+            vn[i][k] = (ok && ((near_mask >> (4 + k)) & 1u)) ? __ldcs(src + (size_t)(k + 1) * t.E + e) : 0.0f;
         }
-        // members of this element's quad among the neighbouring rows: 0 <= a + d <= 3
-        float o[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-        for (int i = 0; i < 4; ++i)
-          if (i == a) o[i] = v;
-        bool lead = true;
-#pragma unroll
-        for (int k = 0; k < 7; ++k) {
-          if (k == 3) continue;
-          const int pos = a + d[k];
-          const bool in = ((near_mask >> k) & 1u) && pos >= 0 && pos <= 3;
-          if (in && k < 3) lead = false;  // a row with a lower flat stores the quad
-          if (in && k > 3) {
-            const float vk = __ldcs(row_grad + (size_t)(m + k - 3) * t.E + e);
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-              if (i == pos) o[i] = vk;
+        for (int i = 0; i < 3; ++i) {
+          const int e = e0 + lane + 32 * i;
+          if (e >= t.E) continue;
+          const long long q = ((long long)b * t.E + e) * (long long)es + j;  // float index in the tensor
+          const int a = (int)(q & 3);
+          if (e == 4 || j - a < 0 || j - a + 3 >= esi) {
+            gp[(size_t)e * es] = v[i];
+            continue;
           }
+          // members of this element's quad among the neighbouring rows: 0 <= a + d <= 3
+          float o[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+          for (int c4 = 0; c4 < 4; ++c4)
+            if (c4 == a) o[c4] = v[i];
+          bool lead = true;
+#pragma unroll
+          for (int k = 0; k < 7; ++k) {
+            if (k == 3) continue;
+            const int pos = a + d[k];
+            const bool in = ((near_mask >> k) & 1u) && pos >= 0 && pos <= 3;
+            if (in && k < 3) lead = false;  // a row with a lower flat stores the quad
+            if (in && k > 3) {
+              const float vk = vn[i][k > 3 ? k - 4 : 0];
+#pragma unroll
+              for (int c4 = 0; c4 < 4; ++c4)
+                if (c4 == pos) o[c4] = vk;
+            }
+          }
+          if (lead)
+            *reinterpret_cast<float4*>(g.grad[l] + (q - a)) = make_float4(o[0], o[1], o[2], o[3]);
         }
-        if (lead)
-          *reinterpret_cast<float4*>(g.grad[l] + (q - a)) = make_float4(o[0], o[1], o[2], o[3]);
       }
     }
   }
