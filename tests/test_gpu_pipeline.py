@@ -100,7 +100,8 @@ def test_grouped_schedule_equals_sequential(dev, name, B, group, monkeypatch):
     targets[1] = []                      # an image without labels inside a range
     gt_h, off_h = yh.pack_labels(targets)
     gt, off = gt_h.to(dev), off_h.to(dev)
-    step = DeviceStep(spec, B, dev, nms_conf=0.3, nms_iou=0.5, by_class=False)
+    step = DeviceStep(spec, B, dev, nms_conf=0.3, nms_iou=0.5, by_class=False, cand_per_image=4096,
+                      max_detections=B * 4096)
     step.run(heads, gt, off)
     seq = snapshot(step)
 
@@ -162,7 +163,8 @@ def test_layered_schedule_equals_sequential(dev, name, B):
     targets[0] = []
     gt_h, off_h = yh.pack_labels(targets)
     gt, off = gt_h.to(dev), off_h.to(dev)
-    step = DeviceStep(spec, B, dev, nms_conf=0.3, nms_iou=0.5, by_class=False)
+    step = DeviceStep(spec, B, dev, nms_conf=0.3, nms_iou=0.5, by_class=False, cand_per_image=4096,
+                      max_detections=B * 4096)
     step.run(heads, gt, off)
     seq = snapshot(step)
 
