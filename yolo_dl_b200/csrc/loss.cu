@@ -1089,15 +1089,17 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
   int dense_grid = ws->num_sms * dense_cps;
   if (dense_grid > slot_room) dense_grid = slot_room;
   int row_grid = ws->num_sms * 4;  // resident in one wave; rows beyond that grid-stride
-  // rows per warp: 8 amortises the scalar box part over the class part when there are rows to
-  // spare; a batch of <= 16 images has ~200 rows per image and is latency-bound — 2 rows per
-  // warp put four times as many warps on the same rows
+  // rows per warp.  The scalar box part runs one row per lane, the class part lanes across C:
+  // more rows per warp amortise the first, fewer put more warps on the same rows (the kernel is
+  // latency-bound).  Inside the overlapped step at 64 images (r2c, same box): 8 -> 177.0 us per
+  // step, 4 -> 167.1, 2 -> 176.5 (alone: 37.7 / 37.1 / 35.1 us); a batch of <= 16 images has
+  // ~200 rows per image and wants every warp it can get: 2 (18.3 -> 9.4 us at 8 images).
   static const int rpw_env = []() {  // sweep knob
     const char* e = getenv("YH_ROWS_PER_WARP");
     const int v = e ? atoi(e) : 0;
     return (v == 2 || v == 4 || v == 8) ? v : 0;
   }();
-  const int rpw = rpw_env ? rpw_env : (B <= 16 ? 2 : kRowsPerWarpMax);
+  const int rpw = rpw_env ? rpw_env : (B <= 16 ? 2 : 4);
   const int rows_per_cta = (kRowThreads / 32) * rpw;
   const int need = (capacity + rows_per_cta - 1) / rows_per_cta;
   if (row_grid > need) row_grid = need;
