@@ -75,8 +75,8 @@ bool pdl_enabled();   // YH_PDL=0/1 forces; default: on for calls on batches of 
 void note_batch(int B);  // the entry points tell the batch size of the call on this thread
 
 template <typename... KArgs, typename... Args>
-inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem,
-                              cudaStream_t s, Args&&... args) {
+inline cudaError_t launch_pdl_if(bool allow, void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                                 cudaStream_t s, Args&&... args) {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid;
   cfg.blockDim = block;
@@ -86,8 +86,16 @@ inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, siz
   at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   at[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = at;
-  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  cfg.numAttrs = (allow && pdl_enabled()) ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
+// Only for a kernel whose stream predecessor is a kernel of THIS library launched by the same
+// entry point (assign_slots -> assign_emit, dense -> rows -> finish, filter -> segment -> emit).
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                              cudaStream_t s, Args&&... args) {
+  return launch_pdl_if(true, kern, grid, block, smem, s, static_cast<Args&&>(args)...);
 }
 
 // ---------------------------------------------------------------------------------

@@ -498,7 +498,7 @@ __device__ __forceinline__ float hausdorff_metric(const Box4 p, const Box4 q, co
 //   phase B  the whole warp walks the rows: lanes across the C class channels (three per lane
 //            up to C = 96, the rest in a tail loop), class BCE forward + backward.
 // Every load of both phases is issued before the first value is consumed.
-constexpr int kRowsPerWarpMax = 8;  // the template parameter RPW of loss_rows_kernel: 8, or 2 for small batches
+// (the template parameter RPW of loss_rows_kernel: 2, 4 or 8 rows per warp)
 constexpr int kClsRegs = 3;
 
 // An image range [b_lo, b_hi) of a batch (yh_loss_*_range): which rows of the (batch, flat)-sorted
@@ -1156,10 +1156,16 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
     const bool bce = p.obj_kind == YH_LOSS_BCE;
     double* part = ws->partials + (size_t)part_off * 4;
     YH_TIME(YH_K_LOSS_DENSE, s);
+    // PDL only behind another dense launch of the same step (a later range / layer part).  The
+    // kernel works BEFORE it waits, so as the first kernel of a call it must not be allowed to
+    // overlap whatever the caller ran last: a captured step whose root node carried the attribute
+    // read labels the preceding copy had not made visible yet (r2c: replay on refilled inputs).
+    const bool dense_pdl = ranged && range->index > 0;
 #define YH_DENSE(G, K)                                                                          \
-  YH_CUDA(launch_pdl(loss_dense_kernel<G, K>, dim3((unsigned)(dense_grid + (G ? dense_tiles : 0))), \
-                     dim3(kDenseThreads), 0, s, dt_tab, dg, Bd, numel, p.w_obj, p.reduction,      \
-                     p.obj_kind, p.gamma, part, dense_grid, dt))
+  YH_CUDA(launch_pdl_if(dense_pdl, loss_dense_kernel<G, K>,                                      \
+                        dim3((unsigned)(dense_grid + (G ? dense_tiles : 0))), dim3(kDenseThreads), 0, \
+                        s, dt_tab, dg, Bd, numel, p.w_obj, p.reduction, p.obj_kind, p.gamma, part, \
+                        dense_grid, dt))
     if (grad_heads) {
       if (bce) YH_DENSE(true, true); else YH_DENSE(true, false);
     } else {
@@ -1190,7 +1196,8 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
     if (direct) rg = g;
     YH_TIME(YH_K_LOSS_ROWS, s);
 #define YH_ROWS(RPW)                                                                            \
-  YH_CUDA(launch_pdl(loss_rows_kernel<RPW>, dim3(row_grid), dim3(kRowThreads), 0, s, tab, rg, p, rr, \
+  YH_CUDA(launch_pdl_if((phases & kPhaseDense) != 0, loss_rows_kernel<RPW>, dim3(row_grid),     \
+                     dim3(kRowThreads), 0, s, tab, rg, p, rr,                                  \
                      (const long long*)m_batch, (const long long*)m_flat, m_target,             \
                      (const long long*)m_class, M_dev, capacity, iou_score_dev, pred_rows_dev,  \
                      (want_grad && !direct) ? ws->row_grad : nullptr, ws->partials))
@@ -1205,7 +1212,8 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
       if (fin_grid > ws->num_sms * 8) fin_grid = ws->num_sms * 8;
     }
     YH_TIME(YH_K_LOSS_FINISH, s);
-    YH_CUDA(launch_pdl(loss_finish_kernel, dim3(fin_grid), dim3(kFinishThreads), 0, s, tab, g, p,
+    YH_CUDA(launch_pdl_if((phases & kPhaseRows) != 0, loss_finish_kernel, dim3(fin_grid),
+                          dim3(kFinishThreads), 0, s, tab, g, p,
                        (const long long*)m_batch, (const long long*)m_flat, M_dev, capacity,
                        grad_heads ? (const float*)ws->row_grad : (const float*)nullptr,
                        (const double*)ws->partials, dense_grid, row_grid, num_ranges,
