@@ -12,7 +12,7 @@ against:
   * the sizes are the ones bench.py measures (YOLOv4-608 batch 64; tiny-416 batch 256; 608
     batch 8), not reduced ones;
   * gradients: the worst element-wise relative error over the significant elements
-    (|g| >= 1e-3 max|g|) is PRINTED and bounded (util.GRAD_REL_SIGNIFICANT).
+    (|g| >= 1e-3 max|g|) is PRINTED next to max|a-b| / max|b|, which util.grad_close bounds.
 Host parts (the f64 matcher, the greedy stand-in for tch-nms) stay on the host as in the reference.
 """
 import numpy as np

@@ -8,10 +8,13 @@ import yolo_dl_b200 as yh
 
 # Tolerances (BASELINE.json north_star: "within 1e-5 relative in fp32").
 # Decoded boxes and loss scalars: |a-b| <= 1e-5*|b| + 1e-7.
-# Gradients: |a-b| <= 1e-5*|b| + 1e-5*max|b|  (element-wise relative error is unbounded where a
-# gradient cancels to ~0; the absolute term is 1e-5 of the tensor's scale).
+# Gradients: |a-b| <= 1e-5*|b| + 4e-6*max|b|.  Element-wise relative error is unbounded where a
+# gradient cancels to ~0 — the reference's own two executors (ATen-CPU, ATen-CUDA) differ by
+# 2.5e-4 relative on elements >= 1e-3*max and by 2.2e-6*max|b| absolutely (printed by
+# tests/test_gpu_aten.py); this library is within 2.3e-6*max|b| of both, the bound is 4e-6.
 RTOL = 1e-5
 ATOL = 1e-7
+GRAD_ATOL_SCALE = 4e-6
 
 
 def close(a, b, rtol=RTOL, atol=ATOL, what=""):
@@ -29,7 +32,7 @@ def close(a, b, rtol=RTOL, atol=ATOL, what=""):
 
 def grad_close(a, b, what=""):
     b_ = torch.as_tensor(b).detach().cpu()
-    close(a, b_, rtol=RTOL, atol=RTOL * float(b_.abs().max()) + 1e-12, what=what)
+    close(a, b_, rtol=RTOL, atol=GRAD_ATOL_SCALE * float(b_.abs().max()) + 1e-12, what=what)
 
 
 def grad_report(a, b, floor=1e-3):
