@@ -139,7 +139,7 @@ int build_layer_tab(const YhLayer* layers, int L, int C, const float* const* hea
   tab->N = (int)expect;
   static const int l2hint = []() {
     const char* e = getenv("YH_L2_HINT");
-    return e ? atoi(e) : 0;
+    return e ? atoi(e) : 1;  // 64-byte fills for the isolated logit loads (filter alone 35.3 -> 32.9 us, r2)
   }();
   tab->l2hint = l2hint;
   return YH_OK;
