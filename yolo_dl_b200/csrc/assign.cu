@@ -66,6 +66,7 @@ __device__ __forceinline__ unsigned cells_of(const AssignTab& t, int l, int a, d
     const double pcx = __dadd_rn((double)cc[i], 0.5) / Wd;
     const double dy = __dsub_rn(gcy, pcy), dx = __dsub_rn(gcx, pcx);
     flat[i] = t.start[l] + (int)cc[i] + t.W[l] * ((int)rr[i] + t.H[l] * a);
+    YH_CHECK(flat[i] >= 0 && flat[i] < t.N);
     d2[i] = (unsigned long long)__double_as_longlong(__dadd_rn(__dmul_rn(dy, dy), __dmul_rn(dx, dx)));
     mask |= 1u << i;
   }
@@ -288,6 +289,7 @@ assign_emit_kernel(int N, int B, const int words, const double* __restrict__ gt,
       while (w) {
         const int bit = __ffs(w) - 1;
         w &= w - 1;
+        YH_CHECK(lp < kEmitList);
         s_list[lp++] = wi * 32 + bit;
       }
     }
@@ -309,7 +311,9 @@ assign_emit_kernel(int N, int B, const int words, const double* __restrict__ gt,
         flat = (tile + lo) * 32 + __ffs(ww) - 1;
       }
       const int pos = base + j;
+      YH_CHECK(flat >= 0 && flat < N);
       const int g = sg[flat];
+      YH_CHECK(g >= 0 && g < gt_off[b + 1] - g0);  // an occupied slot names a label of this image
       sg[flat] = kEmptyGt;
       sd[flat] = ~0ull;
       if (pos < capacity) {

@@ -11,6 +11,18 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+// compute-sanitizer is closed on this pool (operators' decision, B200_PROFILING.md), so the
+// bounds discipline of the kernels with hand-rolled indexing is checked by the kernels themselves:
+// a build with -DYH_BOUNDS (make bounds -> libyolohot_bounds.so) turns every YH_CHECK into a device
+// assert (message + trap -> cudaErrorAssert at the next call), and the whole GPU suite is run once
+// against that library (YH_LIB=..., profiles/r2_bounds_pytest.log).  No cost in the shipped build.
+#ifdef YH_BOUNDS
+#include <assert.h>
+#define YH_CHECK(cond) assert(cond)
+#else
+#define YH_CHECK(cond) ((void)0)
+#endif
+
 #include "yolohot.h"
 
 namespace yh {

@@ -103,6 +103,7 @@ decode_kernel(const LayerTab t, const ChunkTab ct, float* __restrict__ cy, float
         if (++row == H) { row = 0; ++anchor; }
       }
     }
+    YH_CHECK(c0[q] >= 0 && c0[q] + cnt[q] <= run && t.start[l] + c0[q] + cnt[q] <= out_stride);
     const size_t off = (size_t)b * (size_t)out_stride + (size_t)t.start[l] + (size_t)c0[q];
     float* outs[4] = {cy + off, cx + off, h + off, w + off};
 #pragma unroll

@@ -588,6 +588,7 @@ loss_rows_kernel(const LayerTab t, const GradTab g, const LossParams p, const Ro
       const int flat = (int)(first ? pre_f : m_flat[m]);
       cls = (int)(first ? pre_c : m_class[m]);
       tg = first ? pre_t : *reinterpret_cast<const float4*>(m_target + (size_t)m * 4);
+      YH_CHECK(b >= 0 && b < p.B && flat >= 0 && flat < t.N && cls >= 0 && cls < t.C);
       const Cell c = locate(t, flat);
       l = c.layer;
       anchor = c.anchor;
@@ -818,6 +819,7 @@ loss_finish_kernel(const LayerTab t, const GradTab g, const LossParams p,
       }
       const int b = (int)__shfl_sync(0xffffffffu, nb, 3);
       const int flat = __shfl_sync(0xffffffffu, nflat, 3);
+      YH_CHECK(b >= 0 && b < p.B && flat >= 0 && flat < t.N);
       const Cell c = locate(t, flat);
       const int l = c.layer;
       if (l < layer_lo || l >= layer_hi) continue;  // another launch's layers (yh_loss_finish_layers)
@@ -860,6 +862,7 @@ loss_finish_kernel(const LayerTab t, const GradTab g, const LossParams p,
           const long long q = ((long long)b * t.E + e) * (long long)es + j;  // float index in the tensor
           const int a = (int)(q & 3);
           if (e == 4 || j - a < 0 || j - a + 3 >= esi) {
+            YH_CHECK(q >= 0 && q < (long long)p.B * t.E * esi);
             gp[(size_t)e * es] = v[i];
             continue;
           }
@@ -882,8 +885,10 @@ loss_finish_kernel(const LayerTab t, const GradTab g, const LossParams p,
                 if (c4 == pos) o[c4] = vk;
             }
           }
-          if (lead)
+          if (lead) {
+            YH_CHECK(q - a >= 0 && q - a + 3 < (long long)p.B * t.E * esi && ((q - a) & 3) == 0);
             *reinterpret_cast<float4*>(g.grad[l] + (q - a)) = make_float4(o[0], o[1], o[2], o[3]);
+          }
         }
       }
     }

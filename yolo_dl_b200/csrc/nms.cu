@@ -73,6 +73,7 @@ struct HeadBoxes {
   __device__ __forceinline__ void get(int seg, unsigned idx, float4& box, long long& grp) const {
     const int cls = (int)(idx / (unsigned)t.N);
     const int n = (int)(idx - (unsigned)cls * (unsigned)t.N);
+    YH_CHECK(cls < t.C);
     const Cell c = locate(t, n);
     const int l = c.layer;
     const size_t es = (size_t)t.A[l] * (size_t)t.HW[l];
@@ -507,6 +508,7 @@ nms_segment_kernel(const P prov, const SegView v, const double iou_thr) {
     const unsigned kwm = s_keep[ti >> 5];
     if (half == 0 && ((kwm >> (ti & 31)) & 1u)) {
       const int pos = nkept + before + __popc(kwm & ((1u << (ti & 31)) - 1u));
+      YH_CHECK(pos >= 0 && pos < K);
       kept_key[pos] = key;
       kept_box[pos] = box;
       kept_grp[pos] = grp;
@@ -636,6 +638,7 @@ nms_big_kernel(const P prov, const SegView v, const int S, const BigView big,
   const int g = (int)blockIdx.x / csz;      // my group
   const int r = (int)blockIdx.x - g * csz;  // my rank inside it
   if (g >= ngroups) return;                 // left-over CTAs
+  YH_CHECK(ngroups <= kBigGroups && csz >= 1);
   unsigned* ctr = big.sync + g * 32;
   unsigned target = 0;
   unsigned* dead = big.dead + g * 2 * kTileWords;
@@ -675,6 +678,12 @@ nms_big_kernel(const P prov, const SegView v, const int S, const BigView big,
 
       // ---- 1. merge sort (result in `keys`) -------------------------------------------------
       const int ntile = (K + kSortTile - 1) / kSortTile;
+#ifdef YH_BOUNDS
+      {  // the segment's room: its stride, or the distance to the next bucket's offset
+        const long long room = v.seg_off ? (long long)(v.seg_off[seg + 1] - v.seg_off[seg]) : v.stride;
+        YH_CHECK((ntile > 1 ? (long long)ntile * kSortTile : (long long)K) <= room);
+      }
+#endif
       const int Kp = ntile * kSortTile;  // merge passes only when ntile > 1: then Kp <= next_pow2(K), the segment's room
       int npass = 0;
       for (int run = 1; run < ntile; run <<= 1) ++npass;
@@ -885,6 +894,7 @@ nms_big_kernel(const P prov, const SegView v, const int S, const BigView big,
               const unsigned kwm = s_keep[ti >> 5];
               if (half == 0 && ((kwm >> (ti & 31)) & 1u)) {
                 const int lp = nkept + before_k + __popc(kwm & ((1u << (ti & 31)) - 1u));
+                YH_CHECK(lp >= 0 && lp < K);
                 kept_key[lp] = key;
                 kept_box[lp] = box;
                 kept_grp[lp] = grp;
@@ -963,6 +973,7 @@ nms_big_kernel(const P prov, const SegView v, const int S, const BigView big,
                   hit = q_grp[rr] == q_grp[j] && suppresses(br, box_area(br), bj, box_area(bj), iou_thr);
                 }
                 const unsigned m = __ballot_sync(0xffffffffu, hit);
+                YH_CHECK(rr >= 0 && rr < kTile && w >= 0 && w < kTileWords);
                 if (lane == 0) m_in[rr * kTileWords + w] = m;
               } else {
                 if (j < nt) {
