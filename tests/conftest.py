@@ -18,3 +18,11 @@ def dev():
     if not torch.cuda.is_available():
         pytest.skip("no CUDA device")
     return torch.device("cuda:0")
+
+
+def pytest_report_header(config):
+    try:
+        from yolo_dl_b200 import _lib
+        return f"yolohot library: {_lib.LIB_PATH} — {_lib.load().yh_version().decode()}"
+    except Exception as e:  # the CPU suite still reports why
+        return f"yolohot library not loaded: {e}"

@@ -170,7 +170,13 @@ int yh_workspace_reserve_rows(YhWorkspace* ws, int capacity, int C) {
 
 const char* yh_last_error(void) { return yh::g_err; }
 
-const char* yh_version(void) { return "yolohot 0.2 (sm_100a)"; }
+const char* yh_version(void) {
+#ifdef YH_BOUNDS
+  return "yolohot 0.2 (sm_100a, YH_BOUNDS: device asserts on)";
+#else
+  return "yolohot 0.2 (sm_100a)";
+#endif
+}
 
 int64_t yh_launch_count(int reset) {
   int64_t v = yh::g_launches;
