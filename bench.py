@@ -13,11 +13,12 @@ reference's default weights, Rect4 matching, NMS at the shipped thresholds (conf
 train.json5:153-154) per class.  `value` is WEAK scaling (every rank owns its own 64 images; the
 only exchange is the 5 weighted loss scalars); the `strong` record beside it is the literal
 configs[1] — ONE global batch of 64 split over the N GPUs (64/N images each).
-One step = yh_decode_merged + yh_assign + the loss (in L2-sized image ranges: yh_loss_dense_range
--> yh_loss_rows_range per range, then yh_loss_finish_ranges; full head gradient) + yh_nms,
-captured once as a CUDA graph over forked/joined streams (yolo_dl_b200/pipeline.py) and replayed
-per step.  The timed region is `--steps` replays between barrier + synchronize; it is repeated
-`--windows` times back to back and `value` is the median window (all windows are in the line).
+One step = yh_decode_merged + yh_assign + yh_loss_dense + yh_loss_rows_compute + yh_loss_finish (full
+head gradient) + yh_nms = 9 kernels, captured once as a CUDA graph over four forked/joined streams
+(yolo_dl_b200/pipeline.py, schedule "overlapped"; the "grouped" / "layered" schedules that cut the loss
+into L2-sized pieces were measured and are slower) and replayed per step.  The timed
+region is `--steps` replays between barrier + synchronize; it is repeated `--windows` times back to
+back and `value` is the median window (all windows are in the line).
 """
 import argparse
 import ctypes
