@@ -206,6 +206,18 @@ int yh_loss_finish(YhWorkspace* ws, const YhLayer* layers, int L, int B, int C,
                    int capacity, const YhLossCfg* cfg, float* losses4_dev,
                    float* const* grad_heads, void* stream);
 
+/* yh_loss_finish for a caller that has arranged its streams so that
+ *   (1) the kernel enqueued on `stream` right before this call is yh_loss_dense of the same step, and
+ *   (2) yh_assign and yh_loss_rows_compute of the step had COMPLETED (joined by an event) before this
+ *       call was enqueued (yolo_dl_b200/pipeline.py run_overlapped).
+ * The scatter kernel is then launched with programmatic dependent launch: its CTAs arrive while the
+ * dense pass drains, load the match list and the staged gradients, and wait for the dense pass only
+ * before their first store.  Same results as yh_loss_finish.  Violating (2) reads stale rows. */
+int yh_loss_finish_after_dense(YhWorkspace* ws, const YhLayer* layers, int L, int B, int C,
+                               const int64_t* m_batch, const int64_t* m_flat, const int32_t* M_dev,
+                               int capacity, const YhLossCfg* cfg, float* losses4_dev,
+                               float* const* grad_heads, void* stream);
+
 /* The same loss in RANGES of images, for callers that order their streams around the 126 MB L2
  * (yolo_dl_b200/pipeline.py; YoloLoss::forward itself is one sequence, loss_.rs:233-256).  The
  * batch is cut into num_ranges <= 16 contiguous image ranges [b_lo, b_hi) (b_lo a multiple of 4:

@@ -190,6 +190,39 @@ def test_layered_schedule_equals_sequential(dev, name, B):
         check()
 
 
+def test_finish_after_dense_equals_finish(dev, monkeypatch):
+    """yh_loss_finish_after_dense (the scatter launched with PDL behind the dense pass, loads before
+    the wait) gives the bits of yh_loss_finish, eagerly and in a replayed graph on refilled inputs."""
+    monkeypatch.setenv("YH_FINISH_EARLY", "1")
+    spec = synth.yolov4_tiny_416()
+    B = 20
+    heads = [h.to(dev) for h in synth.make_heads(spec, B, 31, obj_mean=-3.5, cls_mean=-2.5)]
+    gt_h, off_h = yh.pack_labels(synth.make_targets(spec, B, 31, n_max=12, clustered=0.3))
+    G = 512
+    gt = torch.zeros((G, 5), dtype=torch.float64, device=dev)
+    gt[:gt_h.shape[0]] = gt_h.to(dev)
+    off = off_h.to(dev)
+    step = DeviceStep(spec, B, dev, nms_conf=0.3, cand_per_image=4096, max_detections=B * 4096)
+    step.run(heads, gt, off)
+    seq = snapshot(step)
+    step.run_overlapped(heads, gt, off)
+    same(seq, snapshot(step))
+    step.capture(heads, gt, off)
+    # new labels and heads in the same buffers
+    for d, h in zip(heads, synth.make_heads(spec, B, 32, obj_mean=-3.5, cls_mean=-2.5)):
+        d.copy_(h)
+    gt2, off2 = yh.pack_labels(synth.make_targets(spec, B, 32, n_max=12))
+    gt[:gt2.shape[0]] = gt2.to(dev)
+    off.copy_(off2)
+    monkeypatch.setenv("YH_FINISH_EARLY", "0")
+    step.run(heads, gt, off)
+    seq2 = snapshot(step)
+    for g in step.grads:
+        g.fill_(float("nan"))
+    step.replay()
+    same(seq2, snapshot(step))
+
+
 def test_graph_replay_follows_refilled_inputs(dev):
     spec = synth.small_spec()
     B = 4

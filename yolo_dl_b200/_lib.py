@@ -70,6 +70,8 @@ SYMBOLS = {
                                      c_void_p, c_void_p, c_int, c_void_p]),
     "yh_loss_finish": (c_int, [c_void_p, POINTER(YhLayer), c_int, c_int, c_int, c_void_p, c_void_p,
                                c_void_p, c_int, POINTER(YhLossCfg), c_void_p, _PF, c_void_p]),
+    "yh_loss_finish_after_dense": (c_int, [c_void_p, POINTER(YhLayer), c_int, c_int, c_int, c_void_p, c_void_p,
+                                           c_void_p, c_int, POINTER(YhLossCfg), c_void_p, _PF, c_void_p]),
     "yh_workspace_reserve_rows": (c_int, [c_void_p, c_int, c_int]),
     "yh_loss_dense_range": (c_int, [c_void_p, _PF, POINTER(YhLayer), c_int, c_int, c_int, c_int, c_int,
                                     c_int, c_int, POINTER(YhLossCfg), _PF, c_void_p]),

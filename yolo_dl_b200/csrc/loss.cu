@@ -793,10 +793,16 @@ loss_finish_kernel(const LayerTab t, const GradTab g, const LossParams p,
                    const float* __restrict__ row_grad, const double* __restrict__ partials,
                    const int dense_per_range, const int rows_per_range, const int num_ranges,
                    const int num_row_ranges, const int range_stride, const int layer_lo,
-                   const int layer_hi, const int do_reduce, float* __restrict__ losses4,
-                   int* __restrict__ err_flag) {
+                   const int layer_hi, const int do_reduce, const int early,
+                   float* __restrict__ losses4, int* __restrict__ err_flag) {
+  // early (yh_loss_finish_after_dense): the stream's previous kernel is the dense pass and
+  // everything this kernel READS (match list, staged row gradients) was complete before it was
+  // enqueued, so with the PDL attribute its CTAs come in while the last wave of the dense pass
+  // drains, load their rows, and only then wait for the dense pass: the stores go out the moment
+  // it has finished instead of a launch + three dependent round trips later (this kernel is the
+  // ~24 us tail of the overlapped step).
   griddep_launch();
-  griddep_wait();
+  if (!early) griddep_wait();
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int warps = kFinishThreads / 32;
   const int M = min(*M_dev, capacity);
@@ -855,6 +861,7 @@ loss_finish_kernel(const LayerTab t, const GradTab g, const LossParams p,
           for (int k = 0; k < 3; ++k)
             vn[i][k] = (ok && ((near_mask >> (4 + k)) & 1u)) ? __ldcs(src + (size_t)(k + 1) * t.E + e) : 0.0f;
         }
+        if (early) griddep_wait();  // from here on: stores over what the dense pass wrote
 #pragma unroll
         for (int i = 0; i < 3; ++i) {
           const int e = e0 + lane + 32 * i;
@@ -894,6 +901,7 @@ loss_finish_kernel(const LayerTab t, const GradTab g, const LossParams p,
     }
   }
   if (blockIdx.x != 0 || !do_reduce) return;
+  if (early) griddep_wait();  // the dense pass's partial sums
 
   // CTA 0: fixed-order final sums
   __shared__ double s_red[kFinishThreads][4];
@@ -984,6 +992,7 @@ struct LossRange {
   int layer_lo, layer_hi;  // dense / finish phase: only these layers (layer_hi <= 0: all)
   int finish_reduce;       // finish phase: also reduce the partial sums (the LAST finish launch)
   int row_ranges;          // finish phase: launches of the rows phase (1: one whole-batch launch)
+  int finish_early;        // finish phase: yh_loss_finish_after_dense (loads before the PDL wait)
 };
 constexpr int kMaxRanges = 16;
 constexpr int kRangeSlots = kPartHalf / kMaxRanges;  // partial-sum slots per ranged launch
@@ -1211,13 +1220,20 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
     YH_LAUNCHED(s);
   }
   if (phases & kPhaseFinish) {
+    const bool fin_early = range != nullptr && range->finish_early;
     int fin_grid = 1;
     if (grad_heads && capacity > 0) {
       fin_grid = (capacity + kFinishThreads / 32 - 1) / (kFinishThreads / 32);
-      if (fin_grid > ws->num_sms * 8) fin_grid = ws->num_sms * 8;
+      // early: a warp per row at most (CTAs beyond the match count exit at once), so that every
+      // row's loads are in flight before the wait; otherwise one resident wave, grid-striding
+      static const bool early_uncapped = []() {
+        const char* e = getenv("YH_FINISH_EARLY_UNCAPPED");
+        return e && e[0] == '1';
+      }();
+      if (!(fin_early && early_uncapped) && fin_grid > ws->num_sms * 8) fin_grid = ws->num_sms * 8;
     }
     YH_TIME(YH_K_LOSS_FINISH, s);
-    YH_CUDA(launch_pdl_if((phases & kPhaseRows) != 0, loss_finish_kernel, dim3(fin_grid),
+    YH_CUDA(launch_pdl_if((phases & kPhaseRows) != 0 || fin_early, loss_finish_kernel, dim3(fin_grid),
                           dim3(kFinishThreads), 0, s, tab, g, p,
                        (const long long*)m_batch, (const long long*)m_flat, M_dev, capacity,
                        grad_heads ? (const float*)ws->row_grad : (const float*)nullptr,
@@ -1225,8 +1241,8 @@ static int loss_phases(int phases, YhWorkspace* ws, const float* const* heads,
                        (ranged && range->row_ranges > 0) ? range->row_ranges : num_ranges, kRangeSlots,
                        (ranged && range->layer_hi > 0) ? range->layer_lo : 0,
                        (ranged && range->layer_hi > 0) ? range->layer_hi : YH_MAX_LAYERS,
-                       (ranged && range->layer_hi > 0) ? range->finish_reduce : 1, losses4_dev,
-                       ws->err_flag));
+                       (ranged && range->layer_hi > 0) ? range->finish_reduce : 1, fin_early ? 1 : 0,
+                       losses4_dev, ws->err_flag));
     YH_LAUNCHED(s);
   }
   return YH_OK;
@@ -1343,6 +1359,18 @@ int yh_loss_finish_layers(YhWorkspace* ws, const YhLayer* layers, int L, int B, 
   YH_REQUIRE(num_dense_parts >= 1 && layer_hi > 0 && layer_lo >= 0 && layer_lo < layer_hi && layer_hi <= L,
              "num_dense_parts=%d layers [%d,%d)", num_dense_parts, layer_lo, layer_hi);
   yh::LossRange r = {0, B, 0, num_dense_parts, nullptr, 0, layer_lo, layer_hi, reduce ? 1 : 0, 1};
+  return yh::loss_phases(yh::kPhaseFinish, ws, nullptr, layers, L, B, C, m_batch, m_flat, nullptr,
+                         nullptr, M_dev, capacity, cfg, losses4_dev, nullptr, nullptr, grad_heads, 0,
+                         stream, &r);
+}
+
+int yh_loss_finish_after_dense(YhWorkspace* ws, const YhLayer* layers, int L, int B, int C,
+                               const int64_t* m_batch, const int64_t* m_flat, const int32_t* M_dev,
+                               int capacity, const YhLossCfg* cfg, float* losses4_dev,
+                               float* const* grad_heads, void* stream) {
+  // the plain whole-batch finish (count 0: not ranged, same partial-sum slots as yh_loss_dense and
+  // yh_loss_rows_compute) with finish_early set
+  yh::LossRange r = {0, B, 0, 0, nullptr, 0, 0, 0, 1, 1, 1};
   return yh::loss_phases(yh::kPhaseFinish, ws, nullptr, layers, L, B, C, m_batch, m_flat, nullptr,
                          nullptr, M_dev, capacity, cfg, losses4_dev, nullptr, nullptr, grad_heads, 0,
                          stream, &r);

@@ -207,7 +207,13 @@ class DeviceStep:
         main.wait_event(joins[1])
         if pub_done is not None:
             main.wait_event(pub_done)
-        _lib.check(self.lib.yh_loss_finish(
+        # YH_FINISH_EARLY=1: the scatter launched into the drain of the dense pass (PDL), its rows
+        # loaded before it waits (yh_loss_finish_after_dense).  Measured, not faster (r2e: 174.2 vs
+        # 174.2-174.9 us per step; with a warp per row instead of one resident wave 191), so off.
+        early = os.environ.get("YH_FINISH_EARLY", "0") == "1" and dense_last \
+            and self._grad_ptrs is not None and pub_done is None
+        fin = self.lib.yh_loss_finish_after_dense if early else self.lib.yh_loss_finish
+        _lib.check(fin(
             self.ws.handle, self.layers, self.L, self.B, self.C, self.m_batch.data_ptr(),
             self.m_flat.data_ptr(), self.M.data_ptr(), self.mcap, self.cfg, self.losses4.data_ptr(),
             self._grad_ptrs, main.cuda_stream))
