@@ -8,7 +8,7 @@ echo "### 2. smoke"; timeout 300 python -c "import __graft_entry__ as g; g.smoke
 echo "### 3. pytest -m gpu"; timeout 2700 python -m pytest tests -m gpu -q -s -p no:cacheprovider > gpurun_out/pytest_gpu.log 2>&1; echo "rc=$?"; tail -25 gpurun_out/pytest_gpu.log | cut -c1-300
 echo "### 4. schedule A/B (B=64)"
 B="python bench.py --steps 300 --warmup 10 --no-cpu-baseline --no-e2e --no-extras --no-strong --windows 3"
-for cfg in "YH_SCHEDULE=overlapped" "YH_ROWS_PER_WARP=4" "YH_ROWS_PER_WARP=2" "YH_L2_HINT=1" "YH_SCHEDULE=overlapped"; do
+for cfg in "YH_SCHEDULE=overlapped" "YH_SCHEDULE=overlapped" "YH_L2_HINT=0"; do
   echo "== $cfg"
   env $cfg timeout 300 $B 2> gpurun_out/bench_err.log | python -c "
 import sys, json
