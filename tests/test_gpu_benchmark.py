@@ -58,3 +58,33 @@ def test_benchmark_no_matches(dev):
     om = odet.forward_merged(heads_cpu, infos, spec.num_classes)
     all_pos = int(om["obj_logit"].sigmoid().ge(0.3).count_nonzero())
     assert got.obj_precision == (0.0 if all_pos else 1.0)
+
+
+def test_benchmark_rejects_null_heads_and_oversized_batch(dev):
+    """yh_benchmark validates like every other head-reading entry point (r1 advisor finding: a NULL
+    `heads` used to reach the kernel as NULL layer pointers and poison the context)."""
+    from yolo_dl_b200 import _lib
+    from yolo_dl_b200.workspace import Workspace
+    spec = synth.small_spec()
+    ws = Workspace()
+    h = ws.ensure(dev, 2, spec.num_instances)
+    infos = yh.MergedDenseDetection.make_info(spec.shapes, spec.anchors)
+    layers = _lib.make_layers(infos)
+    lib = _lib.load()
+    counts = torch.zeros(5, dtype=torch.int64, device=dev)
+    M = torch.zeros(1, dtype=torch.int32, device=dev)
+    rc = lib.yh_benchmark(h, None, layers, len(infos), 2, spec.num_classes, None, None, M.data_ptr(), 0, 0.5,
+                          counts.data_ptr(), None)
+    assert rc == _lib.YH_ERR_INVALID and b"heads is NULL" in lib.yh_last_error()
+    heads = [t.to(dev) for t in synth.make_heads(spec, 4, 3)]
+    rc = lib.yh_benchmark(h, _lib.ptr_array(heads), layers, len(infos), 4, spec.num_classes, None, None,
+                          M.data_ptr(), 0, 0.5, counts.data_ptr(), None)
+    assert rc == _lib.YH_ERR_INVALID and b"max_batch" in lib.yh_last_error()
+    # the context is intact: a valid call still works
+    rc = lib.yh_benchmark(h, _lib.ptr_array([t[:2].contiguous() for t in heads]), layers, len(infos), 2,
+                          spec.num_classes, None, None, M.data_ptr(), 0, 0.5, counts.data_ptr(), None)
+    assert rc == _lib.YH_OK
+    torch.cuda.synchronize()
+    assert int(counts[0]) == 2 * spec.num_instances
+    # the sticky flag's device word is exposed and clear
+    assert lib.yh_workspace_error_flag(h) and ws.read_counts(torch.cuda.current_stream(dev).cuda_stream) == (0, 0)

@@ -5,7 +5,7 @@
 //                                lower index, suppress iff IoU > thr, IoU = inter/(a+b-inter)
 //   YoloInference::forward       yolo-dl/src/loss/inference.rs:50-77 (class pick)
 //
-// Pipeline of yh_nms (3 launches):
+// Pipeline of yh_nms (3 launches; 4 + a memset when the candidate capacity admits large segments):
 //   nms_filter_kernel   one warp per 32 instances.  Reads the objectness plane (4 B/instance);
 //                       only where sigmoid(obj) >= thr — conf = obj*cls <= obj, so nothing else
 //                       can pass (nms.rs:97-99) — the warp reads that instance's C class logits
@@ -13,13 +13,12 @@
 //                       (~ordered(score) << 32 | class*N + instance) to the image's candidate
 //                       list with ONE atomicAdd per ballot.  The [B,C,N] confidence tensor of
 //                       the reference is never materialised.
-//   nms_segment_kernel  one CTA per image: sorts the keys (bitonic; in shared memory up to 8192
-//                       keys, hybrid shared/global above), so the list is in score-descending,
-//                       then nonzero()-index-ascending order, and runs the greedy pass in tiles
-//                       of 1024 candidates: each thread tests its candidate against the kept
-//                       list (shared-memory cache, warp-broadcast reads), then warps resolve
-//                       their 32 candidates in order with ballot/shuffle and publish the newly
-//                       kept boxes to the later warps.  No K x K mask exists anywhere.
+//   nms_segment_kernel  one CTA per segment of <= YH_BIG_MIN candidates: sorts the keys (rank sort
+//                       up to 1024 keys; bitonic in shared memory up to 8192, hybrid above), so
+//                       the list is in score-descending, then nonzero()-index-ascending order,
+//                       and runs the greedy pass in tiles of 512 candidates: test against the
+//                       kept list (shared-memory cache), 512 x 512 suppression bit matrix, one
+//                       warp walks the tile in order.  No K x K mask exists anywhere.
 //                       Per-class suppression only adds "same class" to the predicate, so one
 //                       sorted list per image serves both modes (nms.rs:129-133).
 //   nms_emit_kernel     ordered compaction of the per-image kept lists into the outputs.
@@ -528,24 +527,30 @@ nms_segment_kernel(const P prov, const SegView v, const double iou_thr) {
 // sort + greedy NMS of LARGE segments on all SMs
 // ---------------------------------------------------------------------------------
 // One persistent cooperative launch (one CTA per SM) handles every segment with more than
-// kBigMin candidates.  The grid splits into up to kBigGroups groups of CTAs, each with its own
-// barrier, and the big segments are dealt round-robin to the groups (B = 8 images of 200 000
-// candidates run as 8 concurrent groups of 18 SMs; one segment gets all SMs).  Per segment:
+// kBigMin candidates.  The grid splits into up to kBigGroups groups of >= kBigMinCtas CTAs, each
+// with its own barrier, and the big segments are dealt round-robin to the groups (one segment:
+// all 148 SMs; 8 images of 200 000 candidates: 8 groups of 18 SMs; 256 buckets of 6 000 rows:
+// 37 groups of 4).  Per segment:
 //   1. merge sort: every CTA sorts tiles of 8192 keys in shared memory, then log2(tiles) merge
 //      passes, each output chunk of 8192 located by a merge-path binary search, loaded as a
 //      bitonic sequence (A ascending ++ B descending) and merged in shared memory;
 //   2. gather: the (t,l,b,r) box and group of every candidate in sorted order, once, into a
-//      per-group staging buffer (the head-reading provider decodes them; 148 CTAs re-decoding
-//      every tile would cost more than the tests);
+//      buffer laid out like the key lists (the head-reading provider decodes them; every CTA
+//      re-decoding every tile would cost more than the tests);
 //   3. greedy pass in tiles of 512, software-pipelined over the group barrier: in phase p
-//        * CTAs 1.. of the group test tile p+1 against the boxes kept by tiles < p (kept list
-//          split evenly over the CTAs, two threads per candidate, results OR-ed into a 512-bit
-//          mask with one atomicOr per warp);
-//        * CTA 0 resolves tile p: mask from phase p-1, test against the boxes tile p-1 kept
-//          (still in its shared memory), 512 x 512 suppression bit matrix, in-order walk by one
-//          warp, append — the only serial part, ~20 us per tile of survivors, far less when
-//          most of the tile is already suppressed.
-// 65 536 candidates of ONE group: 617 ms on one CTA (round 1) -> a few ms.
+//        * CTAs 1.. of the group prepare tile p+1 — its test against the boxes kept by tiles < p
+//          (kept list split evenly over the CTAs and staged through shared memory, two threads
+//          per candidate, results OR-ed into a 512-bit mask with one atomicOr per warp), its
+//          512 x 512 in-tile suppression bit matrix and the 512 x 512 matrix "candidate of tile p
+//          suppresses candidate of tile p+1" (both pure functions of the boxes);
+//        * CTA 0 resolves tile p with no IoU arithmetic: alive = ~mask & ~OR(rows of what tile
+//          p-1 kept), register walk over the in-tile matrix (walk_tile), append — the only
+//          serial part, ~10 us per tile.
+//      (The first version did the previous-tile test, the matrix and a shuffle walk on the
+//      resolver: ~170 us per tile of survivors — one SM's worth of IoU arithmetic.)
+// ONE group of 65 536 / 200 000 candidates: 617 ms / - on one CTA (round 1), 21.8 / 50.2 ms with
+// the first version, 3.86 / 13.7 ms now (the kept-list test on all SMs is what remains: ncu SM
+// 39 % busy, 1.66e9 warp instructions, profiles/r2_nms_big_ncu.txt).
 constexpr int kBigThreads = 1024;
 constexpr int kBigMin = YH_BIG_MIN;
 constexpr int kBigGroups = 64;   // most CTA groups one launch splits into (YH_BIG_GROUPS in common.cuh)
