@@ -900,12 +900,10 @@ loss_finish_kernel(const LayerTab t, const GradTab g, const LossParams p,
       }
     }
   }
-  // the LAST CTA reduces: the grid is sized from the capacity, so it usually has no rows to scatter
-  // and the reduction runs beside the scatter instead of behind CTA 0's share of it
-  if (blockIdx.x != gridDim.x - 1 || !do_reduce) return;
+  if (blockIdx.x != 0 || !do_reduce) return;
   if (early) griddep_wait();  // the dense pass's partial sums
 
-  // fixed-order final sums
+  // CTA 0: fixed-order final sums
   __shared__ double s_red[kFinishThreads][4];
   // every thread sums a strided subset; the loads of a thread are independent of its sums,
   // so they are issued kFinalUnroll at a time (the association is still a fixed one)

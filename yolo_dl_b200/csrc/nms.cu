@@ -377,7 +377,7 @@ __device__ __forceinline__ unsigned walk_tile(const unsigned* mask, unsigned rem
   return keep;
 }
 
-template <class P, bool REGWALK>
+template <class P>
 __global__ void __launch_bounds__(kNmsThreads)
 nms_segment_kernel(const P prov, const SegView v, const double iou_thr) {
   extern __shared__ __align__(16) unsigned long long s_keys[];
@@ -473,34 +473,26 @@ nms_segment_kernel(const P prov, const SegView v, const double iou_thr) {
     __syncthreads();
 
     // ---- c. in-order walk, one warp ----------------------------------------------------------
-    // The register walk of nms_big_kernel (walk_tile) costs ~300 cycles per 32-candidate word
-    // whatever is kept, the shuffle walk ~120 cycles per KEPT box.  Inside the overlapped training
-    // step at 64 images the register walk made this kernel 42 us instead of 33 and the step 193 us
-    // instead of 177-180 (same-box A/B of two libraries, profiles/r2_ab_libs.txt) although alone
-    // both take 22.7 us, so it is instantiated only for small batches (REGWALK: B <= 16), where
-    // this kernel sits on the critical path and nothing streams beside it.
+    // (the register walk of nms_big_kernel, walk_tile, is NOT used here: inside the overlapped
+    // training step it made this kernel 42 us instead of 33 and the step 193 us instead of 177-180
+    // — same-box A/B of the two libraries, profiles/r2_ab_libs.txt — although alone both take 22.7 us)
     if (wid == 0) {
-      if (REGWALK) {
-        const unsigned rem0 = (lane < nwords) ? ~(s_al[0][lane] & s_al[1][lane]) : ~0u;
-        s_keep[lane] = walk_tile(mask, rem0, nwords, lane);
-      } else {
-        unsigned rem = (lane < nwords) ? ~(s_al[0][lane] & s_al[1][lane]) : ~0u;
-        unsigned keep = 0u;
-        for (int w = 0; w < nwords; ++w) {
-          unsigned cur = __shfl_sync(0xffffffffu, rem, w);
-          unsigned kw = 0u;
-          while (~cur) {
-            const int j = __ffs(~cur) - 1;
-            kw |= 1u << j;
-            const int r = w * 32 + j;
-            const unsigned mrow = (lane >= w && lane < nwords) ? mask[r * kTileWords + lane] : 0u;
-            rem |= mrow;
-            cur |= __shfl_sync(0xffffffffu, mrow, w) | ((2u << j) - 1u);
-          }
-          if (lane == w) keep = kw;
+      unsigned rem = (lane < nwords) ? ~(s_al[0][lane] & s_al[1][lane]) : ~0u;
+      unsigned keep = 0u;
+      for (int w = 0; w < nwords; ++w) {
+        unsigned cur = __shfl_sync(0xffffffffu, rem, w);
+        unsigned kw = 0u;
+        while (~cur) {
+          const int j = __ffs(~cur) - 1;
+          kw |= 1u << j;
+          const int r = w * 32 + j;
+          const unsigned mrow = (lane >= w && lane < nwords) ? mask[r * kTileWords + lane] : 0u;
+          rem |= mrow;
+          cur |= __shfl_sync(0xffffffffu, mrow, w) | ((2u << j) - 1u);
         }
-        s_keep[lane] = keep;
+        if (lane == w) keep = kw;
       }
+      s_keep[lane] = keep;
     }
     __syncthreads();
 
@@ -1274,16 +1266,14 @@ constexpr int kMaxDevices = 64;
 
 template <class P>
 static int launch_segments(YhWorkspace* ws, const P& prov, SegView v, int S, double iou_thr,
-                           cudaStream_t s, bool small_batch = false) {
+                           cudaStream_t s) {
   static bool seg_attr[kMaxDevices] = {};
   static bool big_attr[kMaxDevices] = {};
   const int dev = ws->device;
   const size_t smem = kSegSmem;
   if (dev >= kMaxDevices || !seg_attr[dev]) {
-    YH_CUDA(cudaFuncSetAttribute(nms_segment_kernel<P, false>,
-                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    YH_CUDA(cudaFuncSetAttribute(nms_segment_kernel<P, true>,
-                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    YH_CUDA(cudaFuncSetAttribute(nms_segment_kernel<P>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)smem));
     if (dev < kMaxDevices) seg_attr[dev] = true;
   }
   // segments above kBigMin candidates need the big buffers; a workspace without them (candidate
@@ -1291,10 +1281,7 @@ static int launch_segments(YhWorkspace* ws, const P& prov, SegView v, int S, dou
   const bool big = ws->big_box != nullptr && v.cap > kBigMin;
   v.big_min = big ? kBigMin : 0;
   YH_TIME(YH_K_NMS_SEGMENT, s);
-  if (small_batch)
-    YH_CUDA(launch_pdl(nms_segment_kernel<P, true>, dim3(S), dim3(kNmsThreads), smem, s, prov, v, iou_thr));
-  else
-    YH_CUDA(launch_pdl(nms_segment_kernel<P, false>, dim3(S), dim3(kNmsThreads), smem, s, prov, v, iou_thr));
+  YH_CUDA(launch_pdl(nms_segment_kernel<P>, dim3(S), dim3(kNmsThreads), smem, s, prov, v, iou_thr));
   YH_LAUNCHED(s);
   if (!big) return YH_OK;
   // the multi-CTA kernel: one CTA per SM, co-resident (cooperative launch: its groups spin on
@@ -1395,7 +1382,7 @@ int yh_nms(YhWorkspace* ws, const float* const* heads, const YhLayer* layers, in
   else YH_FILTER(1);
 #undef YH_FILTER
   YH_LAUNCHED(s);
-  rc = launch_segments(ws, prov, v, B, iou_threshold, s, B <= 16);
+  rc = launch_segments(ws, prov, v, B, iou_threshold, s);
   if (rc) return rc;
   YH_TIME(YH_K_NMS_EMIT, s);
   if (ws->big_box != nullptr && v.cap > kBigMin) {
