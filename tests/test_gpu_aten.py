@@ -144,6 +144,13 @@ def test_nms_yolov4_608_batch8_vs_aten_cuda(dev, by_class, conf_thr, iou_thr):
     _check_nms_aten(dev, synth.yolov4_608(), 8, synth.SEED0, conf_thr, iou_thr, by_class)
 
 
+@pytest.mark.parametrize("by_class", [True, False])
+def test_nms_yolov4_608_batch64_vs_aten_cuda(dev, by_class):
+    """the NMS of the benchmarked step itself: YOLOv4-608, batch 64, conf .4 / IoU .5 (bench.py runs
+    the per-class mode; per image is what the reference's binaries use)."""
+    _check_nms_aten(dev, synth.yolov4_608(), 64, synth.SEED0 + 1, 0.4, 0.5, by_class)
+
+
 @pytest.mark.parametrize("by_class", [False, True])
 @pytest.mark.parametrize("conf_thr,iou_thr", [(0.4, 0.5), (0.1, 0.6)])
 def test_nms_tiny416_batch256_vs_aten_cuda(dev, by_class, conf_thr, iou_thr):
