@@ -353,6 +353,32 @@ int yh_average_precision(const int32_t* det_gt_dev, const double* det_iou_dev,
                          int num_thresholds, int n_points, double* out_ap_dev, void* scratch_dev,
                          size_t scratch_bytes, void* stream);
 
+/* yh_average_precision_static: NO COUNTERPART IN THE REFERENCE — added
+ * for callers that cannot allocate device memory (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid cudaMalloc).  Same kernel, arguments, results and
+ * error behaviour as yh_average_precision, but the per-detection arrays of problems above 8192
+ * detections live in a file-scope `static __device__` array of YH_AP_STATIC_BYTES inside the
+ * library instead of caller scratch; the call allocates and frees nothing.
+ *   limit   yh_average_precision_scratch_bytes(num_problems, max_detections_per_problem) must be
+ *           <= YH_AP_STATIC_BYTES (e.g. one problem of 131 072 detections, or three of 65 536);
+ *           beyond that -> YH_ERR_CAPACITY with a message naming both sizes (use
+ *           yh_average_precision with caller scratch).  Up to 8192 detections per problem the
+ *           array is not touched at all.
+ *   cost    every GPU that loads the library holds the YH_AP_STATIC_BYTES until the process exits.
+ *   sharing every call on a device uses the SAME array, which keeps the last call's contents.
+ *           Nothing in it has to start at zero (the kernel writes each element it reads first),
+ *           but two calls that overlap on the GPU (different streams, or two host threads on one
+ *           device) RACE on it: serialise them, or use yh_average_precision with own scratch.
+ *   set-up  the first call on each device asks cudaGetSymbolAddress for the array's device
+ *           address with that device current (the calling thread's current device must be the one
+ *           `stream` belongs to); later calls reuse it. */
+#define YH_AP_STATIC_BYTES (4u << 20)
+int yh_average_precision_static(const int32_t* det_gt_dev, const double* det_iou_dev,
+                                const double* det_conf_dev, const int32_t* problem_offsets_dev,
+                                const int32_t* num_ground_truth_dev, int num_problems,
+                                int max_detections_per_problem, const double* iou_thresholds_dev,
+                                int num_thresholds, int n_points, double* out_ap_dev, void* stream);
+
 /* ---- §8e: the data-parallel loss exchange as peer-memory stores over NVLink / NVSwitch.
  * Replaces the per-step master-device averaging of the loss scalars
  * (`train/src/train/multi_gpu.rs:188-195`, `yolo-dl/src/loss/loss_.rs:527-577`): sum_g loss_g*B_g /

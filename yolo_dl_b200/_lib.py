@@ -100,6 +100,8 @@ SYMBOLS = {
     "yh_average_precision": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
                                      c_void_p, c_int, c_int, c_void_p, c_void_p, ctypes.c_size_t, c_void_p]),
     "yh_average_precision_scratch_bytes": (ctypes.c_size_t, [c_int, c_int]),
+    "yh_average_precision_static": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
+                                            c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "yh_peer_mailbox_create": (c_int, [c_int, c_int, c_int, POINTER(c_void_p), POINTER(c_void_p),
                                        c_void_p]),
     "yh_peer_mailbox_open": (c_int, [c_int, c_void_p, POINTER(c_void_p)]),

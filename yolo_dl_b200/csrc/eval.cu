@@ -21,6 +21,8 @@
 //                      envelope) and one binary search per interpolation point.
 #include <math.h>
 
+#include <atomic>
+
 #include "common.cuh"
 
 namespace yh {
@@ -380,6 +382,87 @@ int yh_average_precision(const int32_t* det_gt_dev, const double* det_iou_dev,
                                                    iou_thresholds_dev, num_thresholds, n_points,
                                                    out_ap_dev,
                                                    need ? (unsigned char*)scratch_dev : nullptr,
+                                                   need ? ap_array_bytes(P) : (size_t)0);
+  YH_LAUNCHED(s);
+  return YH_OK;
+}
+
+}  // extern "C"
+
+// ---- yh_average_precision_static: the same kernel with its scratch in a file-scope device array.
+// No counterpart in the reference; for callers that cannot allocate (include/yolohot.h).
+namespace yh {
+
+// Every GPU that loads the library holds these YH_AP_STATIC_BYTES until the process exits.
+static __device__ __align__(256) unsigned char g_ap_static[YH_AP_STATIC_BYTES];
+
+constexpr int kApMaxDevices = 64;
+// device address of g_ap_static per device.  In host code `g_ap_static` is only the host-side
+// stand-in of the symbol: the address a kernel may use comes from cudaGetSymbolAddress, asked
+// once per device with that device current.
+static std::atomic<unsigned char*> g_ap_static_ptr[kApMaxDevices];
+
+static int ap_static_address(unsigned char** out) {
+  int dev = 0;
+  YH_CUDA(cudaGetDevice(&dev));
+  YH_REQUIRE(dev >= 0 && dev < kApMaxDevices, "device %d beyond the %d this entry point tracks", dev,
+             kApMaxDevices);
+  unsigned char* p = g_ap_static_ptr[dev].load(std::memory_order_acquire);
+  if (p == nullptr) {
+    void* sym = nullptr;
+    YH_CUDA(cudaGetSymbolAddress(&sym, g_ap_static));
+    YH_REQUIRE(sym != nullptr, "cudaGetSymbolAddress returned NULL for the static scratch");
+    p = static_cast<unsigned char*>(sym);
+    g_ap_static_ptr[dev].store(p, std::memory_order_release);  // racing threads store the same value
+  }
+  *out = p;
+  return YH_OK;
+}
+
+}  // namespace yh
+
+extern "C" {
+
+int yh_average_precision_static(const int32_t* det_gt_dev, const double* det_iou_dev,
+                                const double* det_conf_dev, const int32_t* problem_offsets_dev,
+                                const int32_t* num_ground_truth_dev, int num_problems,
+                                int max_detections_per_problem, const double* iou_thresholds_dev,
+                                int num_thresholds, int n_points, double* out_ap_dev, void* stream) {
+  using namespace yh;
+  YH_REQUIRE(num_problems >= 1 && num_thresholds >= 1, "num_problems=%d num_thresholds=%d",
+             num_problems, num_thresholds);
+  YH_REQUIRE(n_points >= 2 && n_points <= kApThreads, "invalid number of interpolated points %d",
+             n_points);
+  YH_REQUIRE(max_detections_per_problem >= 0 && max_detections_per_problem <= (1 << 30),
+             "max_detections_per_problem=%d", max_detections_per_problem);
+  YH_REQUIRE(problem_offsets_dev && num_ground_truth_dev && iou_thresholds_dev && out_ap_dev,
+             "NULL argument");
+  const int P = ap_pow2(max_detections_per_problem);
+  // same rule as yh_average_precision: up to kApMax detections per problem everything is in
+  // shared memory and the static array is not touched
+  const size_t need = yh_average_precision_scratch_bytes(num_problems, max_detections_per_problem);
+  if (need > (size_t)YH_AP_STATIC_BYTES) {
+    set_error("yh_average_precision_static: %d problems of up to %d detections need %zu bytes of "
+              "scratch, the static array holds %zu (YH_AP_STATIC_BYTES); use yh_average_precision "
+              "with caller scratch",
+              num_problems, max_detections_per_problem, need, (size_t)YH_AP_STATIC_BYTES);
+    return YH_ERR_CAPACITY;
+  }
+  unsigned char* scratch = nullptr;
+  if (need > 0) {
+    const int rc = ap_static_address(&scratch);
+    if (rc != YH_OK) return rc;
+  }
+  // nothing in the array has to start at zero: the kernel writes idx[0,P), best/tp/env[0,D) of a
+  // problem's slice before it reads them, so the previous call's contents are never observed
+  const size_t smem = ap_smem_bytes(P);
+  cudaStream_t s = (cudaStream_t)stream;
+  YH_CUDA(cudaFuncSetAttribute(ap_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  YH_TIME(YH_K_AP, s);
+  ap_kernel<<<num_problems, kApThreads, smem, s>>>(det_gt_dev, det_iou_dev, det_conf_dev,
+                                                   problem_offsets_dev, num_ground_truth_dev,
+                                                   iou_thresholds_dev, num_thresholds, n_points,
+                                                   out_ap_dev, scratch,
                                                    need ? ap_array_bytes(P) : (size_t)0);
   YH_LAUNCHED(s);
   return YH_OK;
