@@ -1,0 +1,27 @@
+#!/bin/bash
+Q="--steps 400 --warmup 10 --no-e2e --no-cpu-baseline --no-extras --no-strong --windows 3"
+python -c "import torch; print('priority range', torch.cuda.Stream.priority_range() if hasattr(torch.cuda.Stream,'priority_range') else 'n/a')"
+run() {
+  echo "== $1"
+  env $1 timeout 200 python bench.py $Q 2>gpurun_out/prio.err | python -c "
+import sys,json
+d=json.loads(sys.stdin.read().strip().splitlines()[-1])
+r=d['roofline']
+print('ms/step',round(d['ms_per_step'],5), [round(x,5) for x in d['value_windows']['ms_per_step']], 'step_frac',round(r['step']['frac'],3))
+print('in_graph', r.get('in_graph', {}).get('span_us'), {k: v['us_sum'] for k, v in r.get('in_graph', {}).get('per_kernel', {}).items()})
+"; tail -2 gpurun_out/prio.err
+}
+run "YH_NMS_PRIO=0 YH_DEC_PRIO=-1"
+run "YH_NMS_PRIO=0 YH_DEC_PRIO=-2 YH_ASG_PRIO=-3"
+run "YH_NMS_PRIO=0 YH_DEC_PRIO=-3 YH_ASG_PRIO=-2"
+run "YH_NMS_PRIO=0 YH_DEC_PRIO=-1 YH_ASG_PRIO=0"
+run "YH_NMS_PRIO=0 YH_DEC_PRIO=-1 YH_DENSE_LAST=0"
+run "YH_NMS_PRIO=-1 YH_DEC_PRIO=-2 YH_ASG_PRIO=-3"
+run "YH_NMS_PRIO=0 YH_DEC_PRIO=-1 YH_MAIN_PRIO=-1"
+run "YH_NMS_PRIO=0 YH_DEC_PRIO=-2 YH_ASG_PRIO=-3 YH_MAIN_PRIO=-1"
+run "YH_NMS_PRIO=0 YH_DEC_PRIO=-1 YH_ROWS_PER_WARP=8"
+run "YH_NMS_PRIO=0 YH_DEC_PRIO=-1 YH_ROWS_PER_WARP=2"
+echo "== timeline NMS 0 DEC -1"
+YH_NMS_PRIO=0 YH_DEC_PRIO=-1 timeout 200 python tools/timeline.py --batch 64 --replays 20 2>&1 | tail -12
+echo "== timeline B=8 NMS 0 DEC -1"
+YH_NMS_PRIO=0 YH_DEC_PRIO=-1 timeout 200 python tools/timeline.py --batch 8 --replays 30 2>&1 | tail -12

@@ -207,6 +207,17 @@ __device__ __forceinline__ double warp_sum_d(double v) {
 // streaming stores / loads: the head gradient is written once and never re-read by us
 __device__ __forceinline__ void st_stream4(float4* p, float4 v) { __stcs(p, v); }
 __device__ __forceinline__ void st_stream1(float* p, float v) { __stcs(p, v); }
+// a store whose line should OUTLIVE the stream around it in the L2 (evict_last priority)
+__device__ __forceinline__ unsigned long long l2_policy_evict_last() {
+  unsigned long long pol;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ void st_keep4(float4* p, float4 v, unsigned long long pol) {
+  asm volatile("st.global.L2::cache_hint.v4.f32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(p), "f"(v.x),
+               "f"(v.y), "f"(v.z), "f"(v.w), "l"(pol)
+               : "memory");
+}
 
 }  // namespace yh
 

@@ -138,6 +138,30 @@ class DeviceStep:
                                    self.ki.data_ptr(), self.tlbr.data_ptr(), self.conf.data_ptr(),
                                    self.K.data_ptr(), self.kcap, s))
 
+    def _side_streams(self):
+        """[decode, assignment + rows, NMS] streams of the fork/join.  The store stream of the dense
+        loss runs on the caller's (default-priority) stream; what the block scheduler does with the
+        other branches is decided by their stream priorities — CTAs of a higher priority are handed
+        out first, equal priorities in launch order — and is worth 11 us of the 171 us step (r2g,
+        profiles/r2g_prio*.txt, same box):
+
+          * more than 16 images: decode and the assignment chain HIGH, the NMS chain DEFAULT.  The
+            candidate filter has thousands of CTAs; on a high-priority stream they took every SM
+            slot for the first 23 us, decode and the dense stream started behind them, decode then
+            crawled under the stream for 115 us and the step was 171 us.  With the filter at the
+            stream's own priority, launched before it, decode (20 us alone) and the filter share
+            the first 40 us, the dense stream then runs nearly undisturbed (93 us in-graph instead
+            of 121), and nms_segment / nms_emit land in the shadow of the scatter at the tail:
+            160 us.  (Filter low but nms_segment / nms_emit high through a per-launch priority
+            attribute: 170 us — they then run UNDER the stream and slow it.  Dense high: 175-181.)
+          * up to 16 images every kernel is latency-bound and the filter is small: all chains HIGH,
+            decode DEFAULT (35.5 us at 8 images against 40 with the setting above).
+
+        YH_DEC_PRIO / YH_ASG_PRIO / YH_NMS_PRIO override (0 default, -1.. higher)."""
+        big = self.B > 16
+        prio = {"YH_DEC_PRIO": -1 if big else 0, "YH_ASG_PRIO": -1, "YH_NMS_PRIO": 0 if big else -1}
+        return [torch.cuda.Stream(self.dev, priority=int(os.environ.get(k, v))) for k, v in prio.items()]
+
     # -- the same 9 kernels as a fork/join over four streams --------------------------------
     def run_overlapped(self, heads, gt_dev, off_dev, publisher=None, lagged_publish=True):
         """The step as the dependency graph it really is (the reference runs it as one sequence,
@@ -157,12 +181,7 @@ class DeviceStep:
         graph (`capture`)."""
         main = torch.cuda.current_stream(self.dev)
         if self._side is None:
-            # decode is bandwidth work (default priority); the assignment and NMS chains are
-            # latency-bound single-CTA-per-image kernels: high priority, so that their few CTAs
-            # are placed as soon as an SM has room
-            self._side = [torch.cuda.Stream(self.dev, priority=int(os.environ.get("YH_DEC_PRIO", "0"))),
-                          torch.cuda.Stream(self.dev, priority=-1),
-                          torch.cuda.Stream(self.dev, priority=int(os.environ.get("YH_NMS_PRIO", "-1")))]
+            self._side = self._side_streams()
         s_dec, s_asg, s_nms = self._side
         hp = _lib.ptr_array(heads)
         fork = torch.cuda.Event()
@@ -320,9 +339,7 @@ class DeviceStep:
         under the dense passes of layers 1-2 instead of after everything."""
         main = torch.cuda.current_stream(self.dev)
         if self._side is None:
-            self._side = [torch.cuda.Stream(self.dev, priority=int(os.environ.get("YH_DEC_PRIO", "0"))),
-                          torch.cuda.Stream(self.dev, priority=-1),
-                          torch.cuda.Stream(self.dev, priority=int(os.environ.get("YH_NMS_PRIO", "-1")))]
+            self._side = self._side_streams()
         if getattr(self, "_fin_streams", None) is None:
             self._fin_streams = [torch.cuda.Stream(self.dev, priority=-1) for _ in range(max(1, self.L - 1))]
         s_dec, s_asg, s_nms = self._side
@@ -412,7 +429,7 @@ class DeviceStep:
             l5[4] = 1.0
         self._loss_ring = [l5[:4] for l5 in self._l5_ring]
         self._graphs = []
-        cap = torch.cuda.Stream(self.dev)
+        cap = torch.cuda.Stream(self.dev, priority=int(os.environ.get("YH_MAIN_PRIO", "0")))
         for k in range(loss_slots):
             self.losses4 = self._loss_ring[k]
             g = torch.cuda.CUDAGraph()
