@@ -35,6 +35,9 @@
 #include <stdlib.h>
 #include <string.h>
 
+#ifdef YH_SEG_PROF
+#include <cstdio>
+#endif
 #include "common.cuh"
 
 namespace yh {
@@ -385,10 +388,20 @@ nms_segment_kernel(const P prov, const SegView v, const double iou_thr) {
   __shared__ long long t_grp[kTile];
   __shared__ unsigned s_al[2][kTileWords];
   __shared__ unsigned s_keep[32];
+  __shared__ unsigned s_nz[kTileWords];  // bit r: row r of the bit matrix has a bit set
   static_assert(kNmsThreads == 2 * kTile, "two threads per candidate of a tile");
 
+#ifdef YH_SEG_PROF  // `make prof`: %globaltimer stamps at the phase boundaries, printed by segment 0
+  unsigned long long T[10];
+  int ti_ = 0;
+#define YH_STAMP() do { if (threadIdx.x == 0 && ti_ < 10) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(T[ti_++])); } while (0)
+#else
+#define YH_STAMP() do { } while (0)
+#endif
+  YH_STAMP();
   griddep_launch();
   griddep_wait();
+  YH_STAMP();
   const int seg = blockIdx.x;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int found = v.count[seg];  // reset to 0 by the emit / rank kernel that follows
@@ -402,8 +415,10 @@ nms_segment_kernel(const P prov, const SegView v, const double iou_thr) {
   float4* kept_box = v.kept_box + seg_base;
   long long* kept_grp = v.kept_grp + seg_base;
 
+  YH_STAMP();
   sort_keys(keys, K, s_keys);
   __syncthreads();
+  YH_STAMP();
 
   // the sort tile becomes the kept-box cache; the bit matrix lives behind it
   float4* c_box = reinterpret_cast<float4*>(s_keys);
@@ -448,11 +463,13 @@ nms_segment_kernel(const P prov, const SegView v, const double iou_thr) {
       t_box[ti] = box;
       t_grp[ti] = grp;
     }
+    if (threadIdx.x < kTileWords) s_nz[threadIdx.x] = 0u;
     {
       const unsigned am = __ballot_sync(0xffffffffu, alive);
       if (lane == 0) s_al[half][wid & (kTileWords - 1)] = am;
     }
     __syncthreads();
+    YH_STAMP();
 
     // ---- b. suppression bits among the survivors (upper triangle) ---------------------------
     for (int item = wid; item < nt * nwords; item += kNmsThreads / 32) {
@@ -468,9 +485,13 @@ nms_segment_kernel(const P prov, const SegView v, const double iou_thr) {
         hit = t_grp[r] == t_grp[j] && suppresses(br, box_area(br), bj, box_area(bj), iou_thr);
       }
       const unsigned m = __ballot_sync(0xffffffffu, hit);
-      if (lane == 0) mask[r * kTileWords + w] = m;
+      if (lane == 0) {
+        mask[r * kTileWords + w] = m;
+        if (m) atomicOr(&s_nz[r >> 5], 1u << (r & 31));
+      }
     }
     __syncthreads();
+    YH_STAMP();
 
     // ---- c. in-order walk, one warp ----------------------------------------------------------
     // (the register walk of nms_big_kernel, walk_tile, is NOT used here: inside the overlapped
@@ -479,22 +500,29 @@ nms_segment_kernel(const P prov, const SegView v, const double iou_thr) {
     if (wid == 0) {
       unsigned rem = (lane < nwords) ? ~(s_al[0][lane] & s_al[1][lane]) : ~0u;
       unsigned keep = 0u;
+      // Only a survivor that suppresses somebody (a row with a bit set: s_nz) needs a step of the
+      // serial chain — a dependent shared-memory load and a shuffle, ~90 ns; the survivors with
+      // empty rows are kept or not by what the others did and cost nothing.  Per-class NMS of a
+      // training step (~50-200 candidates per image over 80 classes: hardly any pair overlaps):
+      // phase c 4.9 -> 1.2 us of the kernel's 12 -> 8.5 (make prof, profiles/r2g_segprof.txt)
       for (int w = 0; w < nwords; ++w) {
         unsigned cur = __shfl_sync(0xffffffffu, rem, w);
-        unsigned kw = 0u;
-        while (~cur) {
-          const int j = __ffs(~cur) - 1;
-          kw |= 1u << j;
+        const unsigned nz = s_nz[w];
+        unsigned t = ~cur & nz;  // alive suppressors of this word, visited in order
+        while (t) {
+          const int j = __ffs(t) - 1;
           const int r = w * 32 + j;
           const unsigned mrow = (lane >= w && lane < nwords) ? mask[r * kTileWords + lane] : 0u;
           rem |= mrow;
-          cur |= __shfl_sync(0xffffffffu, mrow, w) | ((2u << j) - 1u);
+          cur |= __shfl_sync(0xffffffffu, mrow, w);
+          t &= ~cur & ~((2u << j) - 1u);  // suppressed by j, or at / before j: done
         }
-        if (lane == w) keep = kw;
+        if (lane == w) keep = ~cur;
       }
       s_keep[lane] = keep;
     }
     __syncthreads();
+    YH_STAMP();
 
     // ---- d. append the kept candidates in order ----------------------------------------------
     int before = 0, total = 0;
@@ -520,6 +548,15 @@ nms_segment_kernel(const P prov, const SegView v, const double iou_thr) {
     __syncthreads();
   }
   if (threadIdx.x == 0) v.kept_count[seg] = nkept;
+#ifdef YH_SEG_PROF
+  YH_STAMP();
+  if (threadIdx.x == 0 && seg == 0) {
+    printf("SEGPROF seg=%d K=%d kept=%d total=%llu:", seg, K, nkept, T[ti_ - 1] - T[0]);
+    for (int i = 1; i < ti_; ++i) printf(" %llu", T[i] - T[i - 1]);
+    printf(" ns (wait | count | sort | a | b | c | d+end)\n");
+  }
+#endif
+#undef YH_STAMP
 }
 
 

@@ -184,6 +184,7 @@ class DeviceStep:
             self._side = self._side_streams()
         s_dec, s_asg, s_nms = self._side
         hp = _lib.ptr_array(heads)
+        dense_last = os.environ.get("YH_DENSE_LAST", "1") == "1"
         fork = torch.cuda.Event()
         fork.record(main)
         for st in self._side:
@@ -203,7 +204,6 @@ class DeviceStep:
         # enqueue the store stream last: the short latency-bound kernels of the other branches then
         # get their CTAs placed before loss_dense's ~15 400 one-tile CTAs start to stream (tools/timeline.py;
         # r1f: dense first 195.8 us per step, dense last 193.6)
-        dense_last = os.environ.get("YH_DENSE_LAST", "1") == "1"
         if not dense_last:
             _lib.check(self.lib.yh_loss_dense(self.ws.handle, hp, self.layers, self.L, self.B, self.C,
                                               self.cfg, self._grad_ptrs, main.cuda_stream))
