@@ -580,7 +580,11 @@ def run_native(args):
                 "peak_source": peak_src, "algorithmic_bytes_per_launch": alg[dom], "kernel_ms": kern_ms[dom],
                 "note": "frac is on ALGORITHMIC bytes of the kernel timed alone; dram_frac = ncu DRAM bytes of the "
                         "same launch / kernel_ms / peak (part of the gradient is still dirty in the L2 when the "
-                        "kernel ends and is written back under whatever runs next)",
+                        "kernel ends and is written back under whatever runs next: the last YH_KEEP_MB = 64 MB of "
+                        "the stream are stored evict_last on purpose, for the scatter behind it).  frac may exceed "
+                        "1.0 by a few percent: the peak is MEASURED_PEAKS' COPY bandwidth (read + write), this "
+                        "kernel is a pure store stream (bare fills reach 6.9-7.0 TB/s on this GPU, "
+                        "profiles/r1f_fill_bench.txt) and does not have to drain the L2 before it ends",
                 "other_kernels": {n: {"ms": kern_ms[n], "algorithmic_bytes": alg.get(n),
                                       "achieved_GBps": (alg[n] / (kern_ms[n] * 1e-3) / 1e9) if alg.get(n) else None}
                                   for n in kern_ms if n != dom}}

@@ -1032,15 +1032,24 @@ static long long keep_bytes() {
   }();
   return v;
 }
+// Only when the gradient is several times what is kept: a gradient that fits the L2 anyway (up to
+// ~16 images of YOLOv4-608) gains nothing, and its latency-bound step loses ~3 us to the slower
+// stores and the second sweep of the scatter (35.2 -> 38.4 us at 8 images, r2g)
+static bool keep_active(const long long dense_bytes) {
+  return keep_bytes() > 0 && dense_bytes >= 3 * keep_bytes();
+}
 static long long keep_tiles(const long long dense_tiles) {
-  const long long k = keep_bytes() / ((long long)kTileFloats * 4);
-  return k < dense_tiles ? k : dense_tiles;
+  if (!keep_active(dense_tiles * kTileFloats * 4)) return 0;
+  return keep_bytes() / ((long long)kTileFloats * 4);
 }
 // first layer of which at least a quarter lies in the kept tail: the scatter takes the rows of
 // the layers from there on first (YH_MAX_LAYERS: no split)
 static int keep_split_layer(const LayerTab& tab, const int B) {
   long long left = keep_bytes();
   int split = YH_MAX_LAYERS;
+  long long total = 0;
+  for (int l = 0; l < tab.L; ++l) total += (long long)B * tab.A[l] * tab.HW[l] * tab.E * 4;
+  if (!keep_active(total)) return split;
   for (int l = tab.L - 1; l >= 1 && left > 0; --l) {
     const long long bytes = (long long)B * tab.A[l] * tab.HW[l] * tab.E * 4;
     if (left * 4 >= bytes) split = l;
