@@ -14,7 +14,7 @@ train.json5:153-154) per class.  `value` is WEAK scaling (every rank owns its ow
 only exchange is the 5 weighted loss scalars); the `strong` record beside it is the literal
 configs[1] — ONE global batch of 64 split over the N GPUs (64/N images each).
 One step = yh_decode_merged + yh_assign + yh_loss_dense + yh_loss_rows_compute + yh_loss_finish (full
-head gradient) + yh_nms = 9 kernels, captured once as a CUDA graph over four forked/joined streams
+head gradient) + yh_nms = 8 kernels, captured once as a CUDA graph over four forked/joined streams
 (yolo_dl_b200/pipeline.py, schedule "overlapped"; the "grouped" / "layered" schedules that cut the loss
 into L2-sized pieces were measured and are slower) and replayed per step.  The timed
 region is `--steps` replays between barrier + synchronize; it is repeated `--windows` times back to
@@ -365,7 +365,10 @@ def side_configs(dev):
             st._decode(hp, cur(s))
             st._nms(hp, cur(s))
         us = graph_us(dev, tiny)
-        cfg2["per_class" if by_class else "per_image"] = {"us_per_batch": us, "launches_per_batch": 4,
+        n0 = int(st.lib.yh_launch_count(0))
+        tiny()
+        cfg2["per_class" if by_class else "per_image"] = {"us_per_batch": us,
+                                                          "launches_per_batch": int(st.lib.yh_launch_count(0)) - n0,
                                                           "images_per_s": B / (us * 1e-6)}
         del st
     out["yolov4_tiny_416_decode_nms_b256"] = cfg2

@@ -253,6 +253,8 @@ struct YhWorkspace {
   float4* kept_box;               // [max_batch * cand_stride] (t,l,b,r)
   long long* kept_grp;            // [max_batch * cand_stride] suppression group of a kept box
   int* kept_count;                // [max_batch]
+  int* seg_ready;                 // [max_batch + 2] nms_segment_kernel's fused emit: kept count + 1 of
+                                  // every finished image (0 between calls) | finished-CTA ticket
 
   int* by_ints;                   // yh_nms_by_scores buckets: count | off | cursor | kept | total
 

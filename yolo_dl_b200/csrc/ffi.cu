@@ -242,6 +242,7 @@ int yh_workspace_destroy(YhWorkspace* ws) {
   cudaFree(ws->kept_key);
   cudaFree(ws->kept_box);
   cudaFree(ws->kept_count);
+  cudaFree(ws->seg_ready);
   cudaFree(ws->kept_grp);
   cudaFree(ws->by_ints);
   cudaFree(ws->big_box);
@@ -315,6 +316,7 @@ int yh_workspace_create(int device, int max_batch, int64_t max_instances, int ca
   YH_ALLOC(ws->kept_key, cands * sizeof(unsigned long long));
   YH_ALLOC(ws->kept_box, cands * sizeof(float4));
   YH_ALLOC(ws->kept_count, (size_t)max_batch * sizeof(int));
+  YH_ALLOC(ws->seg_ready, ((size_t)max_batch + 2) * sizeof(int));
   YH_ALLOC(ws->kept_grp, cands * sizeof(long long));
   YH_ALLOC(ws->by_ints, 2048 * sizeof(int));
   YH_ALLOC(ws->cand_need, 64);
@@ -332,6 +334,7 @@ int yh_workspace_create(int device, int max_batch, int64_t max_instances, int ca
   if (cudaMemset(ws->slot_dist, 0xff, slots * sizeof(unsigned long long)) != cudaSuccess ||
       cudaMemset(ws->slot_gt, 0x7f, slots * sizeof(int)) != cudaSuccess ||
       cudaMemset(ws->cand_count, 0, (size_t)max_batch * sizeof(int)) != cudaSuccess ||
+      cudaMemset(ws->seg_ready, 0, ((size_t)max_batch + 2) * sizeof(int)) != cudaSuccess ||
       cudaMemset(ws->by_ints, 0, 2048 * sizeof(int)) != cudaSuccess ||
       cudaMemset(ws->ticket, 0, 64) != cudaSuccess ||
       cudaMemset(ws->cand_need, 0, 64) != cudaSuccess ||

@@ -21,7 +21,9 @@
 //                       warp walks the tile in order.  No K x K mask exists anywhere.
 //                       Per-class suppression only adds "same class" to the predicate, so one
 //                       sorted list per image serves both modes (nms.rs:129-133).
-//   nms_emit_kernel     ordered compaction of the per-image kept lists into the outputs.
+//   nms_emit_kernel     ordered compaction of the per-image kept lists into the outputs — behind
+//                       the large-segment kernel only: otherwise nms_segment_kernel emits by
+//                       itself (SegEmit: kept counts published per image, look-back for the base).
 //   nms_big_kernel      segments (an image; a group bucket of yh_nms_by_scores) with more than
 //                       kBigMin candidates: the same greedy pass spread over ALL SMs — merge sort,
 //                       box gather, and per 512-candidate tile the test against the kept list on
@@ -327,6 +329,25 @@ struct SegView {
   int big_min;                   // segments with more candidates belong to nms_big_kernel (0: none do)
 };
 
+// Fused emit (yh_nms without large segments): the segment kernel itself compacts the kept lists
+// into the outputs — the CTA of image s learns its first output row from the kept counts its
+// predecessors publish (ready[i] = kept_i + 1; CTAs are handed out in index order, so the ones a
+// CTA waits for are always resident or done) — instead of a second kernel behind it: one launch
+// and one dependent-kernel gap (~8 us of the NMS chain) less.
+struct SegEmit {
+  int on;             // 0: only the kept lists are produced (yh_nms_by_scores; large segments)
+  int N;              // instances per image (index = class * N + instance)
+  long long* kb;
+  long long* kc;
+  long long* ki;
+  float* tlbr;
+  float* conf;
+  int* out_K;
+  int capacity;
+  int* err_flag;
+  int* ready;         // [S + 2]: kept + 1 per finished image | ticket; all zero between calls
+};
+
 // Greedy pass, in tiles of kTile candidates (score order):
 //   a. every candidate of the tile is tested against the boxes kept by earlier tiles (two
 //      threads per candidate, each walking half of the kept list: shared-memory cache first);
@@ -382,7 +403,7 @@ __device__ __forceinline__ unsigned walk_tile(const unsigned* mask, unsigned rem
 
 template <class P>
 __global__ void __launch_bounds__(kNmsThreads)
-nms_segment_kernel(const P prov, const SegView v, const double iou_thr) {
+nms_segment_kernel(const P prov, const SegView v, const double iou_thr, const SegEmit em) {
   extern __shared__ __align__(16) unsigned long long s_keys[];
   __shared__ float4 t_box[kTile];
   __shared__ long long t_grp[kTile];
@@ -548,6 +569,55 @@ nms_segment_kernel(const P prov, const SegView v, const double iou_thr) {
     __syncthreads();
   }
   if (threadIdx.x == 0) v.kept_count[seg] = nkept;
+  if (em.on) {  // kernel-uniform
+    const int S = (int)gridDim.x;
+    __shared__ int s_esum[kNmsThreads / 32];
+    __shared__ int s_elast;
+    if (threadIdx.x == 0) {
+      v.count[seg] = 0;  // leave the candidate count 0 for the next filter pass
+      asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(em.ready + seg), "r"(nkept + 1) : "memory");
+    }
+    int part = 0;
+    for (int i = threadIdx.x; i < seg; i += kNmsThreads) {
+      int r;
+      do {
+        asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(r) : "l"(em.ready + i) : "memory");
+      } while (r == 0);
+      part += r - 1;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+    if (lane == 0) s_esum[wid] = part;
+    __syncthreads();  // also: this CTA's kept lists (phase d) are visible to all its threads
+    int out_base = 0;
+#pragma unroll
+    for (int k = 0; k < kNmsThreads / 32; ++k) out_base += s_esum[k];
+    if (threadIdx.x == 0 && seg == S - 1) {
+      const int total = out_base + nkept;
+      *em.out_K = min(total, em.capacity);
+      if (total > em.capacity) atomicOr(em.err_flag, 4);
+    }
+    for (int r = threadIdx.x; r < nkept; r += kNmsThreads) {
+      const int pos = out_base + r;
+      if (pos >= em.capacity) break;
+      const unsigned long long kkey = kept_key[r];
+      const unsigned idx = (unsigned)(kkey & 0xffffffffull);
+      const unsigned cls = idx / (unsigned)em.N;
+      em.kb[pos] = seg;
+      em.kc[pos] = (long long)cls;
+      em.ki[pos] = (long long)(idx - cls * (unsigned)em.N);
+      reinterpret_cast<float4*>(em.tlbr)[pos] = kept_box[r];
+      em.conf[pos] = bits_to_score((unsigned)(kkey >> 32));
+    }
+    // the last CTA to get here puts the ready words and the ticket back to zero: every other CTA
+    // has finished its look-back by then
+    __syncthreads();
+    if (threadIdx.x == 0) s_elast = (atomicAdd(em.ready + S, 1) == S - 1) ? 1 : 0;
+    __syncthreads();
+    if (s_elast) {
+      for (int i = threadIdx.x; i <= S; i += kNmsThreads) em.ready[i] = 0;
+    }
+  }
 #ifdef YH_SEG_PROF
   YH_STAMP();
   if (threadIdx.x == 0 && seg == 0) {
@@ -1303,7 +1373,7 @@ constexpr int kMaxDevices = 64;
 
 template <class P>
 static int launch_segments(YhWorkspace* ws, const P& prov, SegView v, int S, double iou_thr,
-                           cudaStream_t s) {
+                           cudaStream_t s, SegEmit em = SegEmit{}) {
   static bool seg_attr[kMaxDevices] = {};
   static bool big_attr[kMaxDevices] = {};
   const int dev = ws->device;
@@ -1318,7 +1388,8 @@ static int launch_segments(YhWorkspace* ws, const P& prov, SegView v, int S, dou
   const bool big = ws->big_box != nullptr && v.cap > kBigMin;
   v.big_min = big ? kBigMin : 0;
   YH_TIME(YH_K_NMS_SEGMENT, s);
-  YH_CUDA(launch_pdl(nms_segment_kernel<P>, dim3(S), dim3(kNmsThreads), smem, s, prov, v, iou_thr));
+  if (big) em.on = 0;  // the large-segment kernel finishes some of the lists: nms_emit_kernel behind it
+  YH_CUDA(launch_pdl(nms_segment_kernel<P>, dim3(S), dim3(kNmsThreads), smem, s, prov, v, iou_thr, em));
   YH_LAUNCHED(s);
   if (!big) return YH_OK;
   // the multi-CTA kernel: one CTA per SM, co-resident (cooperative launch: its groups spin on
@@ -1419,8 +1490,31 @@ int yh_nms(YhWorkspace* ws, const float* const* heads, const YhLayer* layers, in
   else YH_FILTER(1);
 #undef YH_FILTER
   YH_LAUNCHED(s);
-  rc = launch_segments(ws, prov, v, B, iou_threshold, s);
+  // without large segments the segment kernel emits by itself (SegEmit); YH_NMS_FUSE_EMIT=0: the
+  // separate emit kernel as before (A/B)
+  static const bool fuse_emit = []() {
+    const char* e = getenv("YH_NMS_FUSE_EMIT");
+    return !(e && e[0] == '0');
+  }();
+  const bool big_path = ws->big_box != nullptr && v.cap > kBigMin;
+  SegEmit em;
+  memset(&em, 0, sizeof(em));
+  if (fuse_emit && !big_path) {
+    em.on = 1;
+    em.N = prov.t.N;
+    em.kb = (long long*)kb;
+    em.kc = (long long*)kc;
+    em.ki = (long long*)ki;
+    em.tlbr = tlbr;
+    em.conf = conf;
+    em.out_K = out_K_dev;
+    em.capacity = capacity;
+    em.err_flag = ws->err_flag;
+    em.ready = ws->seg_ready;
+  }
+  rc = launch_segments(ws, prov, v, B, iou_threshold, s, em);
   if (rc) return rc;
+  if (em.on) return YH_OK;
   YH_TIME(YH_K_NMS_EMIT, s);
   if (ws->big_box != nullptr && v.cap > kBigMin) {
     // behind the cooperative large-segment kernel: plain launch

@@ -87,12 +87,15 @@ class DeviceStep:
                 "nms_segment_kernel": 24 * detections, "nms_emit_kernel": 32 * detections}
 
     def expected_kernels(self, grouped=None):
-        """kernel launches of one step: decode, 2 assignment, 3 NMS (+1: the large-segment NMS
+        """kernel launches of one step: decode, 2 assignment, 2 NMS (4 with the large-segment NMS
         kernel, launched whenever the candidate capacity admits a segment above YH_BIG_MIN), and
         the loss: dense + rows + finish, or per image range dense + rows, then one finish."""
         grouped = (self.schedule == "grouped" and self._grad_ptrs is not None and self.B >= 8) \
             if grouped is None else grouped
-        base = 6 + (1 if self.ws.key[3] > 1024 else 0)   # YH_BIG_MIN
+        # NMS: filter + segment (which emits by itself) — or, when the candidate capacity admits a
+        # segment above YH_BIG_MIN, filter + segment + large-segment kernel + emit
+        fused = os.environ.get("YH_NMS_FUSE_EMIT", "1") != "0"
+        base = 3 + (4 if self.ws.key[3] > 1024 else (2 if fused else 3))
         if self.schedule == "layered" and self._grad_ptrs is not None and self.L >= 2 and not grouped:
             return base + 1 + 2 * self.L
         if not grouped:
@@ -106,7 +109,7 @@ class DeviceStep:
 
     def run(self, heads: Sequence[torch.Tensor], gt_dev: torch.Tensor, off_dev: torch.Tensor, stream=None):
         """heads: L contiguous f32 CUDA tensors [B, A*(5+C), H, W]; gt_dev [G,5] f64; off_dev [B+1] i32.
-        Enqueues 9 kernels on ONE stream, in the order the reference executes them; nothing
+        Enqueues 8 kernels on ONE stream, in the order the reference executes them; nothing
         synchronises."""
         s = stream if stream is not None else torch.cuda.current_stream(self.dev).cuda_stream
         self._decode(_lib.ptr_array(heads), s)
@@ -162,7 +165,7 @@ class DeviceStep:
         prio = {"YH_DEC_PRIO": -1 if big else 0, "YH_ASG_PRIO": -1, "YH_NMS_PRIO": 0 if big else -1}
         return [torch.cuda.Stream(self.dev, priority=int(os.environ.get(k, v))) for k, v in prio.items()]
 
-    # -- the same 9 kernels as a fork/join over four streams --------------------------------
+    # -- the same 8 kernels as a fork/join over four streams --------------------------------
     def run_overlapped(self, heads, gt_dev, off_dev, publisher=None, lagged_publish=True):
         """The step as the dependency graph it really is (the reference runs it as one sequence,
         train/src/train/single_gpu.rs:152-186):
@@ -170,7 +173,7 @@ class DeviceStep:
             decode                                            (Detect2D x L + merge)
             assign -> loss_rows (staged row gradients) --\
             loss_dense ----------------------------------+--> loss_finish (scatter + reduce)
-            nms_filter -> nms_segment -> nms_emit
+            nms_filter -> nms_segment (emits the kept lists itself)
 
         (YoloLoss fwd+bwd: neither the dense objectness pass nor the matched rows need each
         other; only the few-microsecond scatter of the staged row gradients over the dense
@@ -215,6 +218,17 @@ class DeviceStep:
             self.pred_rows.data_ptr(), 1 if self._grad_ptrs is not None else 0, s_asg.cuda_stream))
         self._nms(hp, s_nms.cuda_stream)
         self._decode(hp, s_dec.cuda_stream)
+        # Above 16 images the dense stream is ordered behind decode.  It costs nothing — the stream
+        # starts at ~40 us anyway, once the filter's CTAs (same priority, launched before it) have
+        # all been handed out, and decode is done at ~31 — and it pins that order: the filter and
+        # the dense pass are both root nodes of the graph, and WHICH of two equal-priority roots the
+        # instantiated graph launches first is not ours to say.  The same step re-captured eight
+        # times in one process: 158.3 / 163.0 us alternating without the edge, 158.1 / 159.6 with
+        # it (profiles/r2g_recapture.txt); dense first is the 176 us schedule.
+        if os.environ.get("YH_DENSE_AFTER_DECODE", "1" if self.B > 16 else "0") == "1":
+            dec_done = torch.cuda.Event()
+            dec_done.record(s_dec)
+            main.wait_event(dec_done)
         if dense_last:
             _lib.check(self.lib.yh_loss_dense(self.ws.handle, hp, self.layers, self.L, self.B, self.C,
                                               self.cfg, self._grad_ptrs, main.cuda_stream))
