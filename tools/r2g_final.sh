@@ -7,7 +7,7 @@ echo "### 1. smoke"; timeout 300 python -c "import __graft_entry__ as g; g.smoke
 echo "### 2. pytest -m gpu"; timeout 2700 python -m pytest tests -m gpu -q -s -p no:cacheprovider > gpurun_out/r2g_pytest_gpu.log 2>&1; echo "rc=$?"; tail -6 gpurun_out/r2g_pytest_gpu.log | cut -c1-300
 echo "### 3. schedule A/B (B=64): r2f settings, then the new defaults, twice"
 B="python bench.py --steps 400 --warmup 10 --no-cpu-baseline --no-e2e --no-extras --no-strong --windows 3"
-for cfg in "YH_DEC_PRIO=0 YH_NMS_PRIO=-1 YH_KEEP_MB=0" "YH_X=0" "YH_DEC_PRIO=0 YH_NMS_PRIO=-1 YH_KEEP_MB=0" "YH_X=0"; do
+for cfg in "YH_DEC_PRIO=0 YH_NMS_PRIO=-1 YH_KEEP_MB=0 YH_NMS_FUSE_EMIT=0 YH_DENSE_AFTER_DECODE=0" "YH_X=0" "YH_DEC_PRIO=0 YH_NMS_PRIO=-1 YH_KEEP_MB=0 YH_NMS_FUSE_EMIT=0 YH_DENSE_AFTER_DECODE=0" "YH_X=0"; do
   echo "== $cfg"
   env $cfg timeout 300 $B 2> gpurun_out/bench_err.log | python -c "
 import sys, json

@@ -141,9 +141,11 @@ template <int kFilterPer>
 __global__ void __launch_bounds__(kFilterThreads)
 nms_filter_kernel(const LayerTab t, const float thr, unsigned long long* __restrict__ keys,
                   const int stride, const int cap, int* __restrict__ count,
-                  int* __restrict__ err_flag) {
+                  int* __restrict__ err_flag, int* __restrict__ seg_ready) {
   griddep_launch();  // nms_segment_kernel's CTAs may take their places while the filter runs
   const int b = blockIdx.y;
+  // the fused emit of nms_segment_kernel (SegEmit) starts from zeroed "kept count published" words
+  if (blockIdx.x == 0 && threadIdx.x == 0) seg_ready[b] = 0;
   const int lane = threadIdx.x & 31;
   const float* hp[kFilterPer];
   unsigned es[kFilterPer];
@@ -345,7 +347,7 @@ struct SegEmit {
   int* out_K;
   int capacity;
   int* err_flag;
-  int* ready;         // [S + 2]: kept + 1 per finished image | ticket; all zero between calls
+  int* ready;         // [S]: kept + 1 of every finished image; zeroed by the filter kernel of the call
 };
 
 // Greedy pass, in tiles of kTile candidates (score order):
@@ -572,17 +574,19 @@ nms_segment_kernel(const P prov, const SegView v, const double iou_thr, const Se
   if (em.on) {  // kernel-uniform
     const int S = (int)gridDim.x;
     __shared__ int s_esum[kNmsThreads / 32];
-    __shared__ int s_elast;
     if (threadIdx.x == 0) {
       v.count[seg] = 0;  // leave the candidate count 0 for the next filter pass
-      asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(em.ready + seg), "r"(nkept + 1) : "memory");
+      // relaxed: the word itself is the whole message (every CTA emits its OWN lists)
+      asm volatile("st.relaxed.gpu.global.s32 [%0], %1;" ::"l"(em.ready + seg), "r"(nkept + 1) : "memory");
     }
     int part = 0;
     for (int i = threadIdx.x; i < seg; i += kNmsThreads) {
       int r;
-      do {
-        asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(r) : "l"(em.ready + i) : "memory");
-      } while (r == 0);
+      for (;;) {
+        asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(r) : "l"(em.ready + i) : "memory");
+        if (r != 0) break;
+        __nanosleep(256);  // 256 images: 32 k pollers on 256 words would crowd the CTAs still working
+      }
       part += r - 1;
     }
 #pragma unroll
@@ -609,14 +613,7 @@ nms_segment_kernel(const P prov, const SegView v, const double iou_thr, const Se
       reinterpret_cast<float4*>(em.tlbr)[pos] = kept_box[r];
       em.conf[pos] = bits_to_score((unsigned)(kkey >> 32));
     }
-    // the last CTA to get here puts the ready words and the ticket back to zero: every other CTA
-    // has finished its look-back by then
-    __syncthreads();
-    if (threadIdx.x == 0) s_elast = (atomicAdd(em.ready + S, 1) == S - 1) ? 1 : 0;
-    __syncthreads();
-    if (s_elast) {
-      for (int i = threadIdx.x; i <= S; i += kNmsThreads) em.ready[i] = 0;
-    }
+    // (the ready words are put back to zero by the NEXT call's filter kernel, nms_filter_kernel)
   }
 #ifdef YH_SEG_PROF
   YH_STAMP();
@@ -1483,7 +1480,7 @@ int yh_nms(YhWorkspace* ws, const float* const* heads, const YhLayer* layers, in
 #define YH_FILTER(P)                                                                          \
   nms_filter_kernel<P><<<grid, kFilterThreads, 0, s>>>(prov.t, (float)confidence_threshold,   \
                                                        v.keys, (int)v.stride, v.cap, v.count, \
-                                                       ws->err_flag)
+                                                       ws->err_flag, ws->seg_ready)
   if (filter_per == 2) YH_FILTER(2);
   else if (filter_per == 4) YH_FILTER(4);
   else if (filter_per == 8) YH_FILTER(8);
@@ -1499,7 +1496,10 @@ int yh_nms(YhWorkspace* ws, const float* const* heads, const YhLayer* layers, in
   const bool big_path = ws->big_box != nullptr && v.cap > kBigMin;
   SegEmit em;
   memset(&em, 0, sizeof(em));
-  if (fuse_emit && !big_path) {
+  // ... and only while every image's CTA is resident at once (one per SM: 57 registers x 1024
+  // threads): with a second wave a CTA that waits for its predecessors also keeps its SM from the
+  // next image (tiny-416 at 256 images: 43 us instead of 33, profiles/r2g_tiny.txt)
+  if (fuse_emit && !big_path && B <= ws->num_sms) {
     em.on = 1;
     em.N = prov.t.N;
     em.kb = (long long*)kb;

@@ -94,7 +94,8 @@ class DeviceStep:
             if grouped is None else grouped
         # NMS: filter + segment (which emits by itself) — or, when the candidate capacity admits a
         # segment above YH_BIG_MIN, filter + segment + large-segment kernel + emit
-        fused = os.environ.get("YH_NMS_FUSE_EMIT", "1") != "0"
+        fused = os.environ.get("YH_NMS_FUSE_EMIT", "1") != "0" and \
+            self.B <= torch.cuda.get_device_properties(self.dev).multi_processor_count
         base = 3 + (4 if self.ws.key[3] > 1024 else (2 if fused else 3))
         if self.schedule == "layered" and self._grad_ptrs is not None and self.L >= 2 and not grouped:
             return base + 1 + 2 * self.L
