@@ -29,11 +29,14 @@ def _stable(merged_ref, thr):
 
 
 def _check_nms(dev, spec, B, seed, conf_thr, iou_thr, by_class, obj_mean=-4.0, cls_mean=-3.0,
-               cand=8192):
+               cand=8192, mutate=None, repeat=1):
     heads_cpu = synth.make_heads(spec, B, seed, obj_mean=obj_mean, cls_mean=cls_mean)
+    if mutate is not None:
+        mutate(heads_cpu)
     heads, _, merged, infos = build(spec, heads_cpu, dev)
     nms = yh.NonMaxSuppressionInit(iou_thr, conf_thr, by_class, max_candidates_per_image=cand).build()
-    out = nms.forward(merged)
+    for _ in range(repeat):  # the same module (workspace) again: the last result is compared
+        out = nms.forward(merged)
     mref = odet.forward_merged(heads_cpu, infos, spec.num_classes)
     _stable(mref, conf_thr)
     ref = onms.nms_forward(mref, conf_thr, iou_thr, by_class)
@@ -75,6 +78,29 @@ def test_nms_tiny416(dev, by_class):
 def test_nms_small_dense(dev, by_class):
     """a head where most cells pass: many candidates per image, several sort tiles."""
     _check_nms(dev, synth.small_spec(), 3, 5, 0.25, 0.45, by_class, obj_mean=1.0, cls_mean=0.5)
+
+
+@pytest.mark.parametrize("by_class", [False, True])
+@pytest.mark.parametrize("name,B", [("yolov4-608", 8), ("yolov4-tiny-416", 32), ("yolov4-tiny-416", 160)])
+def test_nms_small_capacity_emit_paths(dev, name, B, by_class):
+    """Candidate capacity <= 1024 (what a training step uses): no large-segment kernel, so
+    nms_segment_kernel emits the kept lists itself while every image's CTA is resident (B <= SM
+    count: look-back over the kept counts its predecessors publish) and the separate emit kernel
+    runs above that (160 images).  Two images in the middle of the batch have no candidate at all
+    (their CTAs publish a count of zero); called twice: the second call starts from the words the
+    first one left."""
+    spec = synth.SPECS[name]()
+
+    def mute(heads):  # objectness far below any threshold for two images
+        for h in heads:
+            E = 5 + spec.num_classes
+            v = h.view(h.shape[0], E, -1)
+            v[B // 2, 4] = -30.0
+            v[B // 2 + 1, 4] = -30.0
+
+    out, ref = _check_nms(dev, spec, B, 20261108, 0.4, 0.5, by_class, cand=1024, mutate=mute, repeat=2)
+    got_b = out.batches.cpu().numpy()
+    assert out.num_samples() > 0 and not np.isin(got_b, [B // 2, B // 2 + 1]).any()
 
 
 def test_nms_no_candidates(dev):
